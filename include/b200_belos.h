@@ -1,0 +1,183 @@
+/*
+ * b200_belos.h — C-ABI of the B200-native Block GMRES hot path.
+ *
+ * This is the drop-in boundary underneath Belos' plugin surface: the C++ shim
+ * include/B200BelosAdapter.hpp (B200MultiVec : Belos::MultiVec<double>,
+ * B200CrsOp : Belos::Operator<double>) forwards every virtual to one of the
+ * entry points below.  Each entry point cites the reference interface it
+ * replaces (paths relative to the reference tree, packages/...).
+ *
+ * Conventions (mirroring Epetra, epetra/src/Epetra_ConfigDefs.h EPETRA_CHK_ERR):
+ *   - every function returns int: 0 = ok, <0 = error, >0 = warning;
+ *     b200_last_error() returns a static, thread-local message for the last
+ *     non-zero return.  The C++ shim turns non-zero into a Belos exception.
+ *   - handles are opaque; the caller owns them and must destroy them.
+ *   - all multivector storage is FP64, column-major, one leading dimension
+ *     per allocation (ld >= n_local, padded to 32 elements).
+ *   - every call is synchronous from the caller's point of view when it
+ *     returns host data (dot / norm / trans_mv / copy_to_host); all other
+ *     calls are stream-ordered on the context's compute stream.
+ *   - no CPU fallback: without a CUDA device every compute entry point
+ *     returns B200_ERR_NO_DEVICE.
+ */
+#ifndef B200_BELOS_H
+#define B200_BELOS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_ERR_ARG (-1)        /* bad argument (Epetra: -1 / -2 size mismatch) */
+#define B200_ERR_SHAPE (-2)
+#define B200_ERR_CUDA (-3)
+#define B200_ERR_NO_DEVICE (-4)
+#define B200_ERR_NCCL (-5)
+#define B200_ERR_ALIAS (-6)
+#define B200_ERR_UNSUPPORTED (-7)
+#define B200_ERR_TIMEOUT (-8)
+
+/* Belos::NormType (belos/src/BelosTypes.hpp) */
+#define B200_NORM_ONE 0
+#define B200_NORM_TWO 1
+#define B200_NORM_INF 2
+
+typedef struct b200_ctx b200_ctx; /* device, streams, pools, mailboxes, NCCL comm */
+typedef struct b200_mv b200_mv;   /* multivector (owning, or view sharing storage) */
+typedef struct b200_op b200_op;   /* row-block distributed CSR operator */
+
+const char* b200_last_error(void);
+const char* b200_version(void);
+
+/* ------------------------------------------------------------------ context
+ * Replaces Epetra_Comm (epetra/src/Epetra_SerialComm.cpp:117-152,
+ * epetra/src/Epetra_MpiComm.cpp:62,126,154): one context per process/GPU. */
+int b200_ctx_create(int device, b200_ctx** out);
+int b200_ctx_destroy(b200_ctx* ctx);
+int b200_ctx_sync(b200_ctx* ctx);
+/* NCCL communicator (replaces MPI_Comm in Epetra_MpiComm). unique id = 128 bytes. */
+int b200_comm_unique_id(void* id128);
+int b200_ctx_comm_init(b200_ctx* ctx, const void* id128, int nranks, int rank);
+int b200_ctx_rank(const b200_ctx* ctx, int* rank, int* nranks);
+/* seed of the Park-Miller generator behind MvRandom (epetra/src/Epetra_Util.cpp:71-99) */
+int b200_ctx_set_seed(b200_ctx* ctx, unsigned int seed);
+/* counters: kernels launched / host syncs since creation (bench "gpu_launches") */
+int b200_ctx_counters(const b200_ctx* ctx, int64_t* launches, int64_t* syncs);
+/* per-kernel-class device timing (CUDA events on the compute stream).
+ * classes: 0 spmm, 1 trans_mv, 2 times_mat_add_mv, 3 dot/norm, 4 axpby/scale/copy, 5 halo */
+#define B200_NUM_KCLASS 6
+int b200_ctx_timing_enable(b200_ctx* ctx, int on);
+int b200_ctx_timing_read(b200_ctx* ctx, double* ms, int64_t* calls, double* bytes, int reset);
+/* raw stream handle (cudaStream_t) so a host harness can record its own events */
+void* b200_ctx_stream(b200_ctx* ctx);
+/* write >L2-sized scratch buffer (bench hygiene between timed iterations) */
+int b200_ctx_flush_l2(b200_ctx* ctx);
+
+/* -------------------------------------------------------------- multivector
+ * Replaces Belos::EpetraMultiVec / Epetra_MultiVector
+ * (belos/epetra/src/BelosEpetraAdapter.cpp:318-570,
+ *  epetra/src/Epetra_MultiVector.cpp). */
+/* ctor: Epetra_MultiVector(Map, numvecs, zeroOut)  Epetra_MultiVector.cpp:60-80 */
+int b200_mv_create(b200_ctx* ctx, int64_t n_local, int64_t n_global, int64_t row_offset,
+                   int ncols, int zero_out, b200_mv** out);
+int b200_mv_destroy(b200_mv* mv);
+/* Clone: same map, numvecs columns, UNINITIALISED   BelosEpetraAdapter.cpp:361-365 */
+int b200_mv_clone(const b200_mv* mv, int ncols, b200_mv** out);
+/* CloneCopy(index) (index==NULL: all columns)       BelosEpetraAdapter.cpp:368-379 */
+int b200_mv_clone_copy(const b200_mv* mv, const int* index, int nindex, b200_mv** out);
+/* CloneView / CloneViewNonConst(index): shares storage; index may be unordered
+ * and repeated (belos/src/BelosMVOPTester.hpp:197-201)  BelosEpetraAdapter.cpp:382-393 */
+int b200_mv_clone_view(const b200_mv* mv, const int* index, int nindex, b200_mv** out);
+int64_t b200_mv_global_length(const b200_mv* mv); /* GetGlobalLength */
+int64_t b200_mv_local_length(const b200_mv* mv);
+int b200_mv_num_vecs(const b200_mv* mv);          /* GetNumberVecs   */
+b200_ctx* b200_mv_ctx(const b200_mv* mv);
+/* mv <- alpha*A*B + beta*mv ; B is a host column-major brows x bcols block with
+ * leading dimension ldb (Teuchos::SerialDenseMatrix::values()/stride()).
+ * BelosEpetraAdapter.cpp:421-435 -> Epetra_MultiVector::Multiply('N','N') */
+int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv* A, const double* B,
+                             int ldb, int brows, int bcols, double beta);
+/* mv <- alpha*A + beta*B (A, B may alias mv)   BelosEpetraAdapter.cpp:437-452
+ * -> Epetra_MultiVector::Update(a,A,b,B,0.0)  Epetra_MultiVector.cpp:1341-1500 */
+int b200_mv_add_mv(b200_mv* mv, double alpha, const b200_mv* A, double beta, const b200_mv* B);
+/* MvScale(alpha), MvScale(vector)              BelosEpetraAdapter.cpp:454-478 */
+int b200_mv_scale(b200_mv* mv, double alpha);
+int b200_mv_scale_cols(b200_mv* mv, const double* alpha, int nalpha);
+/* B(brows x bcols, ldb) <- alpha * A^T * mv ; honours ldb, never resizes.
+ * BelosEpetraAdapter.cpp:480-495 -> Multiply('T','N') + Reduce()
+ * (Epetra_MultiVector.cpp:1936-2083,2400-2433).  Multi-rank: NCCL allreduce. */
+int b200_mv_trans_mv(const b200_mv* mv, double alpha, const b200_mv* A, double* B, int ldb,
+                     int brows, int bcols);
+/* b[j] <- sum_i mv(i,j)*A(i,j)                 BelosEpetraAdapter.cpp:497-513 */
+int b200_mv_dot(const b200_mv* mv, const b200_mv* A, double* b, int nb);
+/* norms (type = B200_NORM_*)                    BelosEpetraAdapter.cpp:515-545,
+ * Epetra_MultiVector.cpp:1508-1545 (Norm1), 1547-1577 (Norm2), 1580-1630 (NormInf) */
+int b200_mv_norm(const b200_mv* mv, int type, double* normvec, int nnorm);
+/* SetBlock(A, index): mv[:, index[i]] <- A[:, i]  BelosEpetraAdapter.cpp:395-419 */
+int b200_mv_set_block(b200_mv* mv, const b200_mv* A, const int* index, int nindex);
+/* MvRandom: Park-Miller LCG in (-1,1), sequence index = global_row + col*n_global
+ * Epetra_MultiVector.cpp:490-515, Epetra_Util.cpp:71-99 */
+int b200_mv_random(b200_mv* mv);
+/* MvInit(alpha) = PutScalar                      Epetra_MultiVector.cpp:595-608 */
+int b200_mv_init(b200_mv* mv, double alpha);
+/* host <-> device transfer of the local rows (ExtractCopy / ctor from array) */
+int b200_mv_copy_to_host(const b200_mv* mv, double* host, int64_t ldh);
+int b200_mv_copy_from_host(b200_mv* mv, const double* host, int64_t ldh);
+/* raw device pointer of column j and the leading dimension (harness / tests) */
+int b200_mv_device_ptr(const b200_mv* mv, int col, void** ptr, int64_t* ld);
+
+/* ----------------------------------------------------------------- operator
+ * Replaces Epetra_CrsMatrix::Multiply(false, X, Y)
+ * (epetra/src/Epetra_CrsMatrix.cpp:3107-3285; kernels GeneralMV :3315-3413,
+ *  GeneralMM :3486-3585) together with the Epetra_Import halo exchange
+ * (epetra/src/Epetra_DistObject.cpp:226-291, Epetra_MultiVector.cpp:619-913)
+ * and the column-map construction of Epetra_CrsGraph::MakeColMap
+ * (epetra/src/Epetra_CrsGraph.cpp:1348-1524).
+ *
+ * Rows [row_begin,row_end) of an n_global x n_global matrix are given in CSR
+ * with GLOBAL column ids; the row-block partition is the uniform linear map of
+ * Epetra_Map(n,0,comm) (epetra/src/Epetra_BlockMap.cpp:83-90).  The library
+ * builds the local column map (owned columns first, then ghosts grouped by
+ * owner rank, ascending GID), the send/recv lists and the interior/boundary
+ * row split.  Arrays are host pointers and are copied. */
+int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_begin, int64_t row_end,
+                       const int32_t* rowptr, const int64_t* colind_global,
+                       const double* values, b200_op** out);
+int b200_op_destroy(b200_op* op);
+/* y <- A x (trans==0) ; trans!=0 returns B200_ERR_UNSUPPORTED (GMRES never asks;
+ * belos/src/BelosOperator.hpp:141 HasApplyTranspose() == false). x and y must
+ * not alias (Epetra handles X==Y with a temp copy, Epetra_CrsMatrix.cpp:3152;
+ * Belos never does it, belos/src/BelosOperatorTraits.hpp). */
+int b200_op_apply(const b200_op* op, const b200_mv* x, b200_mv* y, int trans);
+int b200_op_info(const b200_op* op, int64_t* n_local, int64_t* n_global, int64_t* nnz_local,
+                 int64_t* n_ghost, int64_t* n_boundary_rows);
+
+/* -------------------------------------------------------- host-side planning
+ * Pure host functions (no device needed) — used by b200_op_create_csr and by
+ * the CPU (gloo) tests of the multi-rank path. */
+/* Epetra_Map(n, 0, comm) linear partition  epetra/src/Epetra_BlockMap.cpp:83-90 */
+int b200_linear_partition(int64_t n_global, int nranks, int rank, int64_t* row_begin,
+                          int64_t* row_end);
+/* MakeColMap: returns number of ghosts; ghost_gids (capacity nnz) filled in local
+ * order, colind_local filled with local ids, ghost_owner per ghost.
+ * epetra/src/Epetra_CrsGraph.cpp:1426-1473 */
+int64_t b200_build_colmap(int64_t n_global, int nranks, int rank, int64_t nnz,
+                          const int64_t* colind_global, int32_t* colind_local,
+                          int64_t* ghost_gids, int32_t* ghost_owner);
+
+/* Galeri-style generators (galeri/src-epetra/Galeri_CrsMatrices.cpp:273-416,
+ * CrsMatrices/Galeri_Cross2D.h, Galeri_Cross3D.h, Galeri_Recirc2D.h;
+ * Brick3D: galeri/src-xpetra/Galeri_XpetraMatrixTypes.hpp:531-633) on the
+ * "Linear" map.  name in {"Laplace2D","Laplace3D","Recirc2D","Brick3D","Tridiag",
+ * "Diag"}; params: conv, diff (Recirc2D), a (Diag value / stencil centre override, 0 = default).
+ * Two-call protocol: rowptr==NULL -> only *nnz is set. */
+int b200_galeri_generate(const char* name, int nx, int ny, int nz, double conv, double diff,
+                         int64_t row_begin, int64_t row_end, int64_t* nnz, int32_t* rowptr,
+                         int64_t* colind_global, double* values);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_BELOS_H */

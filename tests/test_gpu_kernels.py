@@ -1,0 +1,272 @@
+"""Per-kernel parity: CUDA path (through the C-ABI) vs the CPU oracle on the same seeded inputs.
+
+Bar (BASELINE.json north_star): normwise relative error <= 1e-13 for every FP64 kernel; exact
+results where the reference's own MVOPTester demands them (belos/src/BelosMVOPTester.hpp).
+"""
+import numpy as np
+import pytest
+
+import oracle
+import trilinos_b200 as tb
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-13
+
+
+def relerr(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    d = np.linalg.norm((a - b).ravel())
+    s = np.linalg.norm(b.ravel())
+    return d / s if s > 0 else d
+
+
+def rnd(n, k, seed):
+    return np.asfortranarray(np.random.default_rng(seed).uniform(-1, 1, size=(n, k)))
+
+
+SIZES = [1, 3, 31, 32, 33, 127, 1000, 4097, 100003]
+
+
+@pytest.mark.parametrize("n", SIZES)
+@pytest.mark.parametrize("k", [1, 4, 5])
+def test_dot_norm(ctx, n, k):
+    a, b = rnd(n, k, 1), rnd(n, k, 2)
+    A, B = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, b)
+    assert relerr(A.MvDot(B), oracle.dot(a, b)) <= TOL * max(1.0, np.sqrt(n))
+    assert relerr(A.MvDot(A), oracle.dot(a, a)) <= TOL
+    for t in (tb.NORM_ONE, tb.NORM_TWO, tb.NORM_INF):
+        assert relerr(A.MvNorm(t), oracle.norm(a, t)) <= TOL
+    assert np.array_equal(A.MvNorm(tb.NORM_INF), np.abs(a).max(axis=0))  # max is exact
+
+
+@pytest.mark.parametrize("n", [1, 33, 1000, 100003])
+@pytest.mark.parametrize("alpha,beta", [(1.0, 0.0), (0.0, 1.0), (0.0, 0.0), (2.5, -0.75), (1.0, 1.0), (-1.0, 1.0)])
+def test_add_mv(ctx, n, alpha, beta):
+    a, b = rnd(n, 4, 3), rnd(n, 4, 4)
+    A, B = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, b)
+    Y = A.Clone(4)
+    Y.MvAddMv(alpha, A, beta, B)
+    ref = oracle.add_mv(alpha, a, beta, b)
+    y = Y.to_numpy()
+    if alpha == 0.0 or beta == 0.0 or (alpha, beta) == (1.0, 1.0) or (alpha, beta) == (-1.0, 1.0):
+        assert np.array_equal(y, ref)  # a single rounding at most: must be bit-exact
+    else:
+        assert relerr(y, ref) <= TOL
+
+
+def test_add_mv_does_not_read_dropped_operand(ctx):
+    """alpha == 0 / beta == 0 must not propagate NaNs from the other operand
+    (Epetra_MultiVector.cpp:1348-1355; contract in BelosMVOPTester.hpp:838-844)."""
+    n = 1000
+    a = rnd(n, 3, 5)
+    bad = np.full((n, 3), np.nan, order="F")
+    A, Bad = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, bad)
+    Y = A.Clone(3)
+    Y.MvAddMv(1.0, A, 0.0, Bad)
+    assert np.array_equal(Y.to_numpy(), a)
+    Y.MvAddMv(0.0, Bad, 1.0, A)
+    assert np.array_equal(Y.to_numpy(), a)
+
+
+def test_add_mv_aliased(ctx):
+    """LinearProblem::computeCurrResVec calls MvAddMv(-1,R,1,B,R) (BelosLinearProblem.hpp:1207)."""
+    n = 5003
+    r, b = rnd(n, 4, 6), rnd(n, 4, 7)
+    R, B = tb.MultiVec.from_numpy(ctx, r), tb.MultiVec.from_numpy(ctx, b)
+    R.MvAddMv(-1.0, R, 1.0, B)
+    assert np.array_equal(R.to_numpy(), oracle.add_mv(-1.0, r, 1.0, b))
+
+
+@pytest.mark.parametrize("n", [1, 33, 4097, 100003])
+def test_scale_init_random(ctx, n):
+    a = rnd(n, 5, 8)
+    A = tb.MultiVec.from_numpy(ctx, a)
+    A.MvScale(-3.5)
+    assert np.array_equal(A.to_numpy(), oracle.scale_cols(-3.5, a))
+    s = np.array([1.0, 0.0, -2.0, 0.5, 3.0])
+    A.MvScale(s)
+    assert np.array_equal(A.to_numpy(), oracle.scale_cols(s, oracle.scale_cols(-3.5, a)))
+    A.MvInit(7.25)
+    assert np.array_equal(A.to_numpy(), np.full((n, 5), 7.25))
+    ctx.set_seed(12345)
+    A.MvRandom()
+    ref, s1 = oracle.random(12345, n, 5)
+    assert np.array_equal(A.to_numpy(), ref)  # integer LCG + one division: bit-exact
+    A.MvRandom()  # the stream continues where it stopped
+    ref2, _ = oracle.random(s1, n, 5)
+    assert np.array_equal(A.to_numpy(), ref2)
+
+
+@pytest.mark.parametrize("n", [1, 5, 127, 1000, 4097, 100003])
+@pytest.mark.parametrize("p,q", [(1, 1), (3, 1), (4, 4), (5, 3), (7, 5), (33, 4), (40, 8), (100, 4), (9, 16), (64, 2)])
+def test_trans_mv(ctx, n, p, q):
+    a, v = rnd(n, p, 9), rnd(n, q, 10)
+    A, V = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, v)
+    got = V.MvTransMv(1.5, A)
+    ref = oracle.trans_mv(1.5, a, v)
+    assert relerr(got, ref) <= TOL
+    # deterministic: same launch twice gives the same bits
+    assert np.array_equal(got, V.MvTransMv(1.5, A))
+
+
+def test_trans_mv_contract(ctx):
+    """BelosMVOPTester.hpp:792-892: alpha == 0 -> exact zeros; zero operand -> exact zeros;
+    B.stride() honoured, entries outside the p x q block untouched."""
+    n, p, q = 1000, 5, 3
+    a, v = rnd(n, p, 11), rnd(n, q, 12)
+    A, V = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, v)
+    assert np.array_equal(V.MvTransMv(0.0, A), np.zeros((p, q)))
+    Z = V.Clone(q)
+    Z.MvInit(0.0)
+    assert np.array_equal(Z.MvTransMv(1.0, A), np.zeros((p, q)))
+    big = np.full((p + 4, q), -7.0, order="F")
+    V.MvTransMv(1.0, A, big, ldb=p + 4)
+    assert relerr(big[:p], oracle.trans_mv(1.0, a, v)) <= TOL
+    assert np.all(big[p:] == -7.0)
+
+
+@pytest.mark.parametrize("n", [1, 5, 127, 1000, 4097, 100003])
+@pytest.mark.parametrize("p,q", [(1, 1), (3, 1), (4, 4), (5, 3), (7, 5), (33, 4), (40, 8), (300, 4), (9, 16)])
+@pytest.mark.parametrize("alpha,beta", [(-1.0, 1.0), (1.0, 0.0), (0.5, 2.0)])
+def test_times_mat_add_mv(ctx, n, p, q, alpha, beta):
+    a, v, b = rnd(n, p, 13), rnd(n, q, 14), rnd(p, q, 15)
+    A, V = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, v)
+    if beta == 0.0:  # must not read V
+        V = tb.MultiVec.from_numpy(ctx, np.full((n, q), np.nan, order="F"))
+    V.MvTimesMatAddMv(alpha, A, b, beta)
+    ref = oracle.times_mat_add_mv(alpha, a, b, beta, v)
+    assert relerr(V.to_numpy(), ref) <= TOL
+
+
+def test_views_and_setblock(ctx):
+    """index list {0,5,2,2,9}: unordered and repeated (BelosMVOPTester.hpp:197-201)."""
+    n = 777
+    a = rnd(n, 10, 16)
+    A = tb.MultiVec.from_numpy(ctx, a)
+    idx = [0, 5, 2, 2, 9]
+    C1 = A.CloneCopy(idx)
+    assert np.array_equal(C1.to_numpy(), a[:, idx])
+    Vw = A.CloneView(idx)
+    assert np.array_equal(Vw.to_numpy(), a[:, idx])
+    assert Vw.GetNumberVecs() == 5 and Vw.GetGlobalLength() == n
+    assert relerr(Vw.MvNorm(), oracle.norm(a[:, idx])) <= TOL
+    assert relerr(Vw.MvDot(C1), oracle.dot(a[:, idx], a[:, idx])) <= TOL
+    g = rnd(n, 4, 17)
+    G = tb.MultiVec.from_numpy(ctx, g)
+    got = Vw.MvTransMv(1.0, G)
+    assert relerr(got, oracle.trans_mv(1.0, g, a[:, idx])) <= TOL
+    # writing through a view changes the parent; copies stay
+    W = A.CloneViewNonConst([7, 3])
+    W.MvInit(2.0)
+    a2 = a.copy()
+    a2[:, [7, 3]] = 2.0
+    assert np.array_equal(A.to_numpy(), a2)
+    assert np.array_equal(C1.to_numpy(), a[:, idx])
+    blk = rnd(n, 3, 18)
+    A.SetBlock(tb.MultiVec.from_numpy(ctx, blk), [8, 1, 4])
+    a2[:, [8, 1, 4]] = blk
+    assert np.array_equal(A.to_numpy(), a2)
+    # update through non-contiguous A and non-contiguous target
+    b = rnd(5, 2, 19)
+    T = A.CloneViewNonConst([6, 0])
+    T.MvTimesMatAddMv(1.0, C1, b, 1.0)
+    ref = oracle.times_mat_add_mv(1.0, a[:, idx], b, 1.0, a2[:, [6, 0]])
+    assert relerr(T.to_numpy(), ref) <= TOL
+
+
+def test_error_behaviour(ctx):
+    A = tb.MultiVec(ctx, 100, 3)
+    B = tb.MultiVec(ctx, 100, 2)
+    C_ = tb.MultiVec(ctx, 90, 3)
+    with pytest.raises(tb.B200Error):
+        A.MvAddMv(1.0, B, 1.0, B)
+    with pytest.raises(tb.B200Error):
+        A.MvAddMv(1.0, C_, 1.0, C_)
+    with pytest.raises(tb.B200Error):
+        A.MvScale([1.0, 2.0])
+    with pytest.raises(tb.B200Error):
+        A.CloneView([0, 3])
+    with pytest.raises(tb.B200Error):
+        A.MvTimesMatAddMv(1.0, B, np.zeros((3, 3)), 0.0)
+
+
+MATS = [("Laplace2D", (100, 100, 1)), ("Laplace3D", (20, 21, 22)), ("Brick3D", (15, 14, 13)), ("Recirc2D", (64, 50, 1)),
+        ("Tridiag", (1000, 1, 1)), ("Laplace3D", (3, 1, 1)), ("Laplace3D", (40, 40, 40))]
+
+
+@pytest.mark.parametrize("name,dims", MATS)
+@pytest.mark.parametrize("k", [1, 2, 4, 5, 8, 16])
+def test_apply(ctx, name, dims, k):
+    n, rp, ci, va = oracle.galeri_csr(name, *dims)
+    op = tb.CrsOperator(ctx, n, 0, n, rp, ci, va)
+    x = rnd(n, k, 20)
+    X = tb.MultiVec.from_numpy(ctx, x)
+    Y = X.Clone(k)
+    Y.MvInit(np.nan)  # result must not depend on the prior contents of Y (MVOPTester.hpp:1454-1600)
+    op.Apply(X, Y)
+    ref = oracle.spmm(rp, ci.astype(np.int32), va, x)
+    assert relerr(Y.to_numpy(), ref) <= TOL
+    assert np.array_equal(X.to_numpy(), x)
+    Z = X.Clone(k)
+    Z.MvInit(0.0)
+    op.Apply(Z, Y)
+    assert np.array_equal(Y.to_numpy(), np.zeros((n, k)))  # OP*0 == 0 exactly
+
+
+def test_apply_wide_rows(ctx):
+    """rows longer than one shared-memory stage (4096 nonzeros) and empty rows."""
+    rng = np.random.default_rng(21)
+    n = 600
+    import scipy.sparse as sp
+    A = sp.random(n, n, density=0.02, random_state=3, format="lil")
+    A[5, :] = rng.uniform(-1, 1, n)
+    A[300, :] = rng.uniform(-1, 1, n)
+    A[7, :] = 0
+    A = A.tocsr()
+    A.sort_indices()
+    A = sp.vstack([A] * 1).tocsr()
+    # make one CTA's segment exceed the stage: 256 dense rows
+    D = sp.csr_matrix(rng.uniform(-1, 1, (256, n)))
+    A = sp.vstack([D, A[256:]]).tocsr()
+    A.sort_indices()
+    op = tb.CrsOperator(ctx, n, 0, n, A.indptr, A.indices.astype(np.int64), A.data)
+    x = rnd(n, 4, 22)
+    X = tb.MultiVec.from_numpy(ctx, x)
+    Y = X.Clone(4)
+    op.Apply(X, Y)
+    assert relerr(Y.to_numpy(), oracle.spmm(A.indptr, A.indices, A.data, x)) <= TOL
+
+
+def test_full_size_properties(ctx):
+    """BASELINE config 2 sizes (n = 1e6, b = 4, basis width 200): size-independent properties."""
+    n, p, q = 1_000_000, 200, 4
+    ctx.set_seed(7)
+    Q = tb.MultiVec(ctx, n, p, zero=False)
+    Q.MvRandom()
+    X = tb.MultiVec(ctx, n, q, zero=False)
+    X.MvRandom()
+    G = X.MvTransMv(1.0, Q)
+    # Gram block agrees with column-wise dots (two different kernels)
+    for j in (0, 57, 199):
+        Qj = Q.CloneView([j] * q)
+        assert relerr(X.MvDot(Qj), G[j]) <= 1e-12
+    # linearity: (Q^T (2X)) == 2 (Q^T X) exactly (power-of-two scaling)
+    X2 = X.CloneCopy()
+    X2.MvScale(2.0)
+    assert np.array_equal(X2.MvTransMv(1.0, Q), 2.0 * G)
+    # projection: X - Q (Q^T X) / ... : update then Gram against an orthogonal-ish basis shrinks
+    n2 = X.MvNorm()
+    X.MvTimesMatAddMv(0.0, Q, G, 1.0)  # alpha = 0: X unchanged
+    assert np.array_equal(X.MvNorm(), n2)
+    # update consistency: X + Q*E(j) picks column j
+    E = np.zeros((p, q))
+    E[3, 0] = 1.0
+    Y = X.CloneCopy()
+    Y.MvTimesMatAddMv(1.0, Q, E, 1.0)
+    Y.MvAddMv(1.0, Y, -1.0, X)
+    q3 = Q.CloneView([3])
+    y0 = Y.CloneView([0])
+    d = y0.CloneCopy()
+    d.MvAddMv(1.0, y0, -1.0, q3)
+    assert d.MvNorm()[0] <= 1e-12 * q3.MvNorm()[0]
+    assert np.all(Y.CloneView([1, 2, 3]).MvNorm() == 0.0)

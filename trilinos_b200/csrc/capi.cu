@@ -1,0 +1,708 @@
+// C-ABI entry points for multivectors and the CSR operator (include/b200_belos.h).
+// Host-side logic only: argument checks with Epetra's error conventions, view/run
+// bookkeeping, staging of the small dense blocks, halo choreography.  All arithmetic on the
+// n-sized data happens in the kernels of elementwise.cu / reduce.cu / gram.cu / update.cu /
+// spmm.cu; there is no host fallback.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+#include "runtime.cuh"
+
+namespace b200 {
+int nccl_allreduce_i64(Ctx* ctx, int64_t* buf, size_t count, cudaStream_t s);
+int nccl_group_start(Ctx* ctx);
+int nccl_group_end(Ctx* ctx);
+int nccl_send(Ctx* ctx, const void* buf, size_t count, bool f64, int peer, cudaStream_t s);
+int nccl_recv(Ctx* ctx, void* buf, size_t count, bool f64, int peer, cudaStream_t s);
+}  // namespace b200
+
+using namespace b200;
+
+namespace {
+
+inline int64_t padded_ld(int64_t n) {
+  int64_t ld = (std::max<int64_t>(n, 1) + kLdAlign - 1) / kLdAlign * kLdAlign;
+  return ld;
+}
+
+int new_mv(Ctx* ctx, int64_t n_local, int64_t n_global, int64_t row_offset, int ncols,
+           b200_mv** out) {
+  if (ncols < 0 || n_local < 0) return fail(B200_ERR_ARG, "multivector: negative size");
+  auto* m = new b200_mv();
+  m->ctx = ctx;
+  m->n_local = n_local;
+  m->n_global = n_global;
+  m->row_offset = row_offset;
+  m->ld = padded_ld(n_local);
+  const size_t bytes = (size_t)m->ld * std::max(ncols, 1) * sizeof(double);
+  void* p = nullptr;
+  int rc = ctx->alloc(bytes, &p);
+  if (rc) {
+    delete m;
+    return rc;
+  }
+  m->st = std::make_shared<Storage>(ctx, (double*)p, bytes);
+  m->cols.resize(ncols);
+  std::iota(m->cols.begin(), m->cols.end(), 0);
+  *out = m;
+  return 0;
+}
+
+inline bool same_map(const MV* a, const MV* b) {
+  return a->ctx == b->ctx && a->n_local == b->n_local && a->n_global == b->n_global;
+}
+
+bool columns_overlap(const MV* a, const MV* b) {
+  if (a->st.get() != b->st.get()) return false;
+  for (int ca : a->cols)
+    for (int cb : b->cols)
+      if (ca == cb) return true;
+  return false;
+}
+
+// Park-Miller jump: seed * 16807^e mod (2^31-1)
+unsigned int pm_advance(unsigned int seed, unsigned long long e) {
+  unsigned long long r = seed % 2147483647ull, base = 16807ull;
+  while (e) {
+    if (e & 1ull) r = (r * base) % 2147483647ull;
+    base = (base * base) % 2147483647ull;
+    e >>= 1;
+  }
+  return (unsigned int)r;
+}
+
+}  // namespace
+
+// =========================================================================== multivector
+extern "C" int b200_mv_create(b200_ctx* ctx, int64_t n_local, int64_t n_global,
+                              int64_t row_offset, int ncols, int zero_out, b200_mv** out) {
+  if (!ctx || !out) return fail(B200_ERR_ARG, "b200_mv_create: null argument");
+  if (n_global < n_local) return fail(B200_ERR_ARG, "b200_mv_create: n_global < n_local");
+  B200_TRY(new_mv(ctx, n_local, n_global, row_offset, ncols, out));
+  if (zero_out && ncols > 0)
+    B200_CUDA(cudaMemsetAsync((*out)->st->ptr, 0, (size_t)(*out)->ld * ncols * sizeof(double),
+                              ctx->stream));
+  return 0;
+}
+
+extern "C" int b200_mv_destroy(b200_mv* mv) {
+  delete mv;
+  return 0;
+}
+
+extern "C" int b200_mv_clone(const b200_mv* mv, int ncols, b200_mv** out) {
+  if (!mv || !out) return fail(B200_ERR_ARG, "b200_mv_clone: null argument");
+  return new_mv(mv->ctx, mv->n_local, mv->n_global, mv->row_offset, ncols, out);
+}
+
+static int check_index(const b200_mv* mv, const int* index, int nindex, const char* who) {
+  if (nindex < 0 || (nindex > 0 && !index)) return failf(B200_ERR_ARG, "%s: bad index list", who);
+  for (int i = 0; i < nindex; ++i)
+    if (index[i] < 0 || index[i] >= mv->ncols())
+      return failf(B200_ERR_ARG, "%s: index[%d]=%d out of range [0,%d)", who, i, index[i],
+                   mv->ncols());
+  return 0;
+}
+
+extern "C" int b200_mv_clone_view(const b200_mv* mv, const int* index, int nindex,
+                                  b200_mv** out) {
+  if (!mv || !out) return fail(B200_ERR_ARG, "b200_mv_clone_view: null argument");
+  B200_TRY(check_index(mv, index, nindex, "CloneView"));
+  auto* v = new b200_mv();
+  v->ctx = mv->ctx;
+  v->st = mv->st;
+  v->n_local = mv->n_local;
+  v->n_global = mv->n_global;
+  v->row_offset = mv->row_offset;
+  v->ld = mv->ld;
+  v->cols.resize(nindex);
+  for (int i = 0; i < nindex; ++i) v->cols[i] = mv->cols[index[i]];
+  *out = v;
+  return 0;
+}
+
+extern "C" int b200_mv_clone_copy(const b200_mv* mv, const int* index, int nindex,
+                                  b200_mv** out) {
+  if (!mv || !out) return fail(B200_ERR_ARG, "b200_mv_clone_copy: null argument");
+  std::vector<int> all;
+  if (!index) {
+    all.resize(mv->ncols());
+    std::iota(all.begin(), all.end(), 0);
+    index = all.data();
+    nindex = (int)all.size();
+  }
+  B200_TRY(check_index(mv, index, nindex, "CloneCopy"));
+  b200_mv* c = nullptr;
+  B200_TRY(new_mv(mv->ctx, mv->n_local, mv->n_global, mv->row_offset, nindex, &c));
+  // copy maximal runs of consecutive source columns
+  int j = 0;
+  while (j < nindex) {
+    int len = 1;
+    while (j + len < nindex && mv->cols[index[j + len]] == mv->cols[index[j + len - 1]] + 1) ++len;
+    int rc = launch_axpby(mv->ctx, c->col(j), c->ld, mv->col(index[j]), mv->ld, nullptr, 0,
+                          mv->n_local, len, 1.0, 0.0);
+    if (rc) {
+      delete c;
+      return rc;
+    }
+    j += len;
+  }
+  *out = c;
+  return 0;
+}
+
+extern "C" int64_t b200_mv_global_length(const b200_mv* mv) { return mv ? mv->n_global : -1; }
+extern "C" int64_t b200_mv_local_length(const b200_mv* mv) { return mv ? mv->n_local : -1; }
+extern "C" int b200_mv_num_vecs(const b200_mv* mv) { return mv ? mv->ncols() : -1; }
+extern "C" b200_ctx* b200_mv_ctx(const b200_mv* mv) {
+  return mv ? static_cast<b200_ctx*>(mv->ctx) : nullptr;
+}
+
+extern "C" int b200_mv_init(b200_mv* mv, double alpha) {
+  if (!mv) return fail(B200_ERR_ARG, "MvInit: null multivector");
+  for (int j = 0; j < mv->ncols();) {
+    const int len = run_length(j, mv->ncols(), mv, j);
+    B200_TRY(launch_fill(mv->ctx, mv->col(j), mv->ld, mv->n_local, len, alpha));
+    j += len;
+  }
+  return 0;
+}
+
+extern "C" int b200_mv_random(b200_mv* mv) {
+  if (!mv) return fail(B200_ERR_ARG, "MvRandom: null multivector");
+  Ctx* ctx = mv->ctx;
+  for (int j = 0; j < mv->ncols();) {
+    const int len = run_length(j, mv->ncols(), mv, j);
+    B200_TRY(launch_random(ctx, mv->col(j), mv->ld, mv->n_local, len, mv->row_offset,
+                           mv->n_global, (int64_t)j * mv->n_global, ctx->seed));
+    j += len;
+  }
+  ctx->seed = pm_advance(ctx->seed, (unsigned long long)mv->n_global * mv->ncols());
+  return 0;
+}
+
+extern "C" int b200_mv_add_mv(b200_mv* mv, double alpha, const b200_mv* A, double beta,
+                              const b200_mv* B) {
+  if (!mv || !A || !B) return fail(B200_ERR_ARG, "MvAddMv: null multivector");
+  // Epetra_MultiVector::Update returns -1 on column mismatch, -2 on length mismatch
+  if (A->ncols() != mv->ncols() || B->ncols() != mv->ncols())
+    return fail(B200_ERR_ARG, "MvAddMv: number of vectors differs (Epetra Update: -1)");
+  if (!same_map(mv, A) || !same_map(mv, B))
+    return fail(B200_ERR_SHAPE, "MvAddMv: vector lengths differ (Epetra Update: -2)");
+  Ctx* ctx = mv->ctx;
+  const int k = mv->ncols();
+  const int64_t n = mv->n_local;
+  // alpha == 0 / beta == 0 short-circuits must not read the dropped operand
+  // (epetra/src/Epetra_MultiVector.cpp:1348-1355)
+  for (int j = 0; j < k;) {
+    const int len = run_length(j, k, mv, j, A, j, B, j);
+    if (alpha == 0.0 && beta == 0.0) {
+      B200_TRY(launch_fill(ctx, mv->col(j), mv->ld, n, len, 0.0));
+    } else if (alpha == 0.0) {
+      if (!(beta == 1.0 && B->col(j) == mv->col(j)))
+        B200_TRY(launch_axpby(ctx, mv->col(j), mv->ld, B->col(j), B->ld, nullptr, 0, n, len, beta,
+                              0.0));
+    } else if (beta == 0.0) {
+      if (!(alpha == 1.0 && A->col(j) == mv->col(j)))
+        B200_TRY(launch_axpby(ctx, mv->col(j), mv->ld, A->col(j), A->ld, nullptr, 0, n, len,
+                              alpha, 0.0));
+    } else {
+      B200_TRY(launch_axpby(ctx, mv->col(j), mv->ld, A->col(j), A->ld, B->col(j), B->ld, n, len,
+                            alpha, beta));
+    }
+    j += len;
+  }
+  return 0;
+}
+
+extern "C" int b200_mv_scale(b200_mv* mv, double alpha) {
+  if (!mv) return fail(B200_ERR_ARG, "MvScale: null multivector");
+  if (alpha == 1.0) return 0;
+  for (int j = 0; j < mv->ncols();) {
+    const int len = run_length(j, mv->ncols(), mv, j);
+    B200_TRY(launch_axpby(mv->ctx, mv->col(j), mv->ld, mv->col(j), mv->ld, nullptr, 0,
+                          mv->n_local, len, alpha, 0.0));
+    j += len;
+  }
+  return 0;
+}
+
+extern "C" int b200_mv_scale_cols(b200_mv* mv, const double* alpha, int nalpha) {
+  if (!mv || !alpha) return fail(B200_ERR_ARG, "MvScale: null argument");
+  if (nalpha != mv->ncols())
+    return failf(B200_ERR_ARG,
+                 "MvScale: vector of scaling factors has length %d, multivector has %d columns",
+                 nalpha, mv->ncols());
+  for (int j = 0; j < mv->ncols();) {
+    const int len = run_length(j, mv->ncols(), mv, j);
+    B200_TRY(launch_scale_cols(mv->ctx, mv->col(j), mv->ld, mv->n_local, len, alpha + j));
+    j += len;
+  }
+  return 0;
+}
+
+extern "C" int b200_mv_set_block(b200_mv* mv, const b200_mv* A, const int* index, int nindex) {
+  if (!mv || !A) return fail(B200_ERR_ARG, "SetBlock: null multivector");
+  B200_TRY(check_index(mv, index, nindex, "SetBlock"));
+  if (A->ncols() < nindex) return fail(B200_ERR_ARG, "SetBlock: A has fewer columns than index");
+  if (!same_map(mv, A)) return fail(B200_ERR_SHAPE, "SetBlock: vector lengths differ");
+  int j = 0;
+  while (j < nindex) {
+    int len = 1;
+    while (j + len < nindex && mv->cols[index[j + len]] == mv->cols[index[j + len - 1]] + 1 &&
+           A->cols[j + len] == A->cols[j + len - 1] + 1)
+      ++len;
+    if (mv->col(index[j]) != A->col(j))
+      B200_TRY(launch_axpby(mv->ctx, mv->col(index[j]), mv->ld, A->col(j), A->ld, nullptr, 0,
+                            mv->n_local, len, 1.0, 0.0));
+    j += len;
+  }
+  return 0;
+}
+
+extern "C" int b200_mv_dot(const b200_mv* mv, const b200_mv* A, double* b, int nb) {
+  if (!mv || !A || !b) return fail(B200_ERR_ARG, "MvDot: null argument");
+  if (A->ncols() != mv->ncols()) return fail(B200_ERR_ARG, "MvDot: number of vectors differs");
+  if (!same_map(mv, A)) return fail(B200_ERR_SHAPE, "MvDot: vector lengths differ");
+  const int k = mv->ncols();
+  if (nb < k) return 0;  // reference silently does nothing (BelosEpetraAdapter.cpp:505)
+  if (k == 0) return 0;
+  Ctx* ctx = mv->ctx;
+  ++ctx->seq;
+  for (int j = 0; j < k;) {
+    const int len = run_length(j, k, mv, j, A, j);
+    B200_TRY(launch_dot(ctx, mv->col(j), mv->ld, A->col(j), A->ld, mv->n_local, len, j,
+                        j + len >= k));
+    j += len;
+  }
+  B200_TRY(ctx->finish_reduction(k, false));
+  for (int j = 0; j < k; ++j) b[j] = ctx->mbox_h[j];
+  return 0;
+}
+
+extern "C" int b200_mv_norm(const b200_mv* mv, int type, double* normvec, int nnorm) {
+  if (!mv || !normvec) return fail(B200_ERR_ARG, "MvNorm: null argument");
+  if (type != B200_NORM_ONE && type != B200_NORM_TWO && type != B200_NORM_INF)
+    return fail(B200_ERR_ARG, "MvNorm: invalid norm type (valid: OneNorm, TwoNorm, InfNorm)");
+  const int k = mv->ncols();
+  if (nnorm < k) return 0;  // reference silently does nothing (BelosEpetraAdapter.cpp:516)
+  if (k == 0) return 0;
+  Ctx* ctx = mv->ctx;
+  ++ctx->seq;
+  for (int j = 0; j < k;) {
+    const int len = run_length(j, k, mv, j);
+    B200_TRY(launch_norm(ctx, mv->col(j), mv->ld, mv->n_local, len, type, j, j + len >= k));
+    j += len;
+  }
+  B200_TRY(ctx->finish_reduction(k, type == B200_NORM_INF));
+  for (int j = 0; j < k; ++j)
+    normvec[j] = (type == B200_NORM_TWO) ? std::sqrt(ctx->mbox_h[j]) : ctx->mbox_h[j];
+  return 0;
+}
+
+extern "C" int b200_mv_trans_mv(const b200_mv* mv, double alpha, const b200_mv* A, double* B,
+                                int ldb, int brows, int bcols) {
+  if (!mv || !A || !B) return fail(B200_ERR_ARG, "MvTransMv: null argument");
+  const int p = A->ncols(), q = mv->ncols();
+  if (brows != p || bcols != q || ldb < std::max(1, brows))
+    return failf(B200_ERR_ARG, "MvTransMv: B is %d x %d (ld %d) but A^T*mv is %d x %d", brows,
+                 bcols, ldb, p, q);
+  if (!same_map(mv, A)) return fail(B200_ERR_SHAPE, "MvTransMv: vector lengths differ");
+  if (p == 0 || q == 0) return 0;
+  if (alpha == 0.0) {  // DGEMM semantics: operands are not referenced
+    for (int j = 0; j < q; ++j)
+      for (int i = 0; i < p; ++i) B[(size_t)j * ldb + i] = 0.0;
+    return 0;
+  }
+  if ((size_t)p * q > kMailboxDoubles)
+    return fail(B200_ERR_ARG, "MvTransMv: result block larger than the host mailbox");
+  Ctx* ctx = mv->ctx;
+  ++ctx->seq;
+  for (int jv = 0; jv < q;) {
+    const int lv = run_length(jv, q, mv, jv);
+    for (int ja = 0; ja < p;) {
+      const int la = run_length(ja, p, A, ja);
+      const bool last = (jv + lv >= q) && (ja + la >= p);
+      B200_TRY(launch_gram(ctx, A->col(ja), A->ld, la, mv->col(jv), mv->ld, lv, mv->n_local,
+                           alpha, ja + jv * p, p, last));
+      ja += la;
+    }
+    jv += lv;
+  }
+  B200_TRY(ctx->finish_reduction(p * q, false));
+  for (int j = 0; j < q; ++j)
+    std::memcpy(B + (size_t)j * ldb, ctx->mbox_h + (size_t)j * p, sizeof(double) * p);
+  return 0;
+}
+
+extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv* A,
+                                        const double* B, int ldb, int brows, int bcols,
+                                        double beta) {
+  if (!mv || !A || !B) return fail(B200_ERR_ARG, "MvTimesMatAddMv: null argument");
+  const int p = A->ncols(), q = mv->ncols();
+  if (brows != p || bcols != q || ldb < std::max(1, brows))
+    return failf(B200_ERR_ARG, "MvTimesMatAddMv: B is %d x %d (ld %d) but A has %d and mv %d columns",
+                 brows, bcols, ldb, p, q);
+  if (!same_map(mv, A)) return fail(B200_ERR_SHAPE, "MvTimesMatAddMv: vector lengths differ");
+  if (q == 0) return 0;
+  Ctx* ctx = mv->ctx;
+  if (alpha == 0.0 || p == 0) {
+    if (beta == 0.0) return b200_mv_init(mv, 0.0);
+    return b200_mv_scale(mv, beta);
+  }
+  if (columns_overlap(mv, A))
+    return fail(B200_ERR_ALIAS, "MvTimesMatAddMv: A and mv share columns (DGEMM forbids aliasing)");
+  const size_t bytes = (size_t)p * q * sizeof(double);
+  if (bytes > kStageSlotBytes)
+    return fail(B200_ERR_ARG, "MvTimesMatAddMv: dense block larger than the staging slot");
+  // stage B (compact p x q) through the pinned ring, then one async H2D copy
+  const int slot = ctx->stage_next;
+  ctx->stage_next = (slot + 1) % kStageSlots;
+  if (ctx->stage_used[slot]) B200_CUDA(cudaEventSynchronize(ctx->stage_ev[slot]));
+  double* hs = (double*)(ctx->stage_h + (size_t)slot * kStageSlotBytes);
+  for (int j = 0; j < q; ++j)
+    std::memcpy(hs + (size_t)j * p, B + (size_t)j * ldb, sizeof(double) * p);
+  B200_CUDA(cudaMemcpyAsync(ctx->dB, hs, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  B200_CUDA(cudaEventRecord(ctx->stage_ev[slot], ctx->stream));
+  ctx->stage_used[slot] = true;
+  for (int jv = 0; jv < q;) {
+    const int lv = run_length(jv, q, mv, jv);
+    bool first = true;
+    for (int ja = 0; ja < p;) {
+      const int la = run_length(ja, p, A, ja);
+      B200_TRY(launch_update(ctx, mv->col(jv), mv->ld, lv, A->col(ja), A->ld, la, mv->n_local,
+                             ctx->dB + ja + (size_t)jv * p, p, alpha, first ? beta : 1.0));
+      first = false;
+      ja += la;
+    }
+    jv += lv;
+  }
+  return 0;
+}
+
+extern "C" int b200_mv_copy_to_host(const b200_mv* mv, double* host, int64_t ldh) {
+  if (!mv || !host) return fail(B200_ERR_ARG, "copy_to_host: null argument");
+  if (ldh < mv->n_local) return fail(B200_ERR_ARG, "copy_to_host: ldh < local length");
+  Ctx* ctx = mv->ctx;
+  if (mv->n_local > 0) {
+    for (int j = 0; j < mv->ncols();) {
+      const int len = run_length(j, mv->ncols(), mv, j);
+      B200_CUDA(cudaMemcpy2DAsync(host + (size_t)j * ldh, (size_t)ldh * 8, mv->col(j),
+                                  (size_t)mv->ld * 8, (size_t)mv->n_local * 8, len,
+                                  cudaMemcpyDeviceToHost, ctx->stream));
+      j += len;
+    }
+  }
+  B200_CUDA(cudaStreamSynchronize(ctx->stream));
+  ++ctx->syncs;
+  return 0;
+}
+
+extern "C" int b200_mv_copy_from_host(b200_mv* mv, const double* host, int64_t ldh) {
+  if (!mv || !host) return fail(B200_ERR_ARG, "copy_from_host: null argument");
+  if (ldh < mv->n_local) return fail(B200_ERR_ARG, "copy_from_host: ldh < local length");
+  Ctx* ctx = mv->ctx;
+  if (mv->n_local > 0) {
+    for (int j = 0; j < mv->ncols();) {
+      const int len = run_length(j, mv->ncols(), mv, j);
+      B200_CUDA(cudaMemcpy2DAsync(mv->col(j), (size_t)mv->ld * 8, host + (size_t)j * ldh,
+                                  (size_t)ldh * 8, (size_t)mv->n_local * 8, len,
+                                  cudaMemcpyHostToDevice, ctx->stream));
+      j += len;
+    }
+  }
+  B200_CUDA(cudaStreamSynchronize(ctx->stream));
+  ++ctx->syncs;
+  return 0;
+}
+
+extern "C" int b200_mv_device_ptr(const b200_mv* mv, int col, void** ptr, int64_t* ld) {
+  if (!mv || col < 0 || col >= mv->ncols()) return fail(B200_ERR_ARG, "device_ptr: bad column");
+  if (ptr) *ptr = mv->col(col);
+  if (ld) *ld = mv->ld;
+  return 0;
+}
+
+// =========================================================================== operator
+namespace {
+
+template <class T>
+int upload(T** dst, const std::vector<T>& src) {
+  *dst = nullptr;
+  const size_t bytes = std::max<size_t>(src.size(), 1) * sizeof(T);
+  B200_CUDA(cudaMalloc((void**)dst, bytes));
+  if (!src.empty())
+    B200_CUDA(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_begin,
+                                  int64_t row_end, const int32_t* rowptr,
+                                  const int64_t* colind_global, const double* values,
+                                  b200_op** out) {
+  if (!ctx || !rowptr || !out) return fail(B200_ERR_ARG, "b200_op_create_csr: null argument");
+  int64_t rb, re;
+  B200_TRY(b200_linear_partition(n_global, ctx->nranks, ctx->rank, &rb, &re));
+  if (rb != row_begin || re != row_end)
+    return failf(B200_ERR_ARG,
+                 "b200_op_create_csr: rows [%lld,%lld) are not this rank's block [%lld,%lld) of "
+                 "the linear map",
+                 (long long)row_begin, (long long)row_end, (long long)rb, (long long)re);
+  const int64_t n_local = re - rb;
+  const int64_t nnz = rowptr[n_local];
+  if (nnz > 0 && (!colind_global || !values))
+    return fail(B200_ERR_ARG, "b200_op_create_csr: null column / value array");
+  B200_CUDA(cudaSetDevice(ctx->device));
+
+  std::vector<int32_t> col_local((size_t)nnz);
+  std::vector<int64_t> ghost_gids((size_t)nnz);
+  std::vector<int32_t> ghost_owner((size_t)nnz);
+  const int64_t n_ghost = b200_build_colmap(n_global, ctx->nranks, ctx->rank, nnz, colind_global,
+                                            col_local.data(), ghost_gids.data(),
+                                            ghost_owner.data());
+  if (n_ghost < 0) return B200_ERR_ARG;
+  ghost_gids.resize((size_t)n_ghost);
+  ghost_owner.resize((size_t)n_ghost);
+
+  // rows sorted by local column id, as after Epetra_CrsGraph::SortIndices/OptimizeStorage
+  std::vector<double> vals(values, values + nnz);
+  std::vector<int32_t> rp(rowptr, rowptr + n_local + 1);
+  std::vector<int32_t> bnd, perm;
+  int max_row = 0;
+  for (int64_t r = 0; r < n_local; ++r) {
+    const int32_t b = rp[r], e = rp[r + 1];
+    if (e < b) return fail(B200_ERR_ARG, "b200_op_create_csr: rowptr not monotone");
+    max_row = std::max(max_row, e - b);
+    bool sorted = true, ghost = false;
+    for (int32_t k = b; k < e; ++k) {
+      if (k > b && col_local[k] < col_local[k - 1]) sorted = false;
+      if (col_local[k] >= n_local) ghost = true;
+    }
+    if (!sorted) {
+      perm.resize(e - b);
+      std::iota(perm.begin(), perm.end(), 0);
+      std::stable_sort(perm.begin(), perm.end(),
+                       [&](int a, int c) { return col_local[b + a] < col_local[b + c]; });
+      std::vector<int32_t> tc(e - b);
+      std::vector<double> tv(e - b);
+      for (int i = 0; i < e - b; ++i) {
+        tc[i] = col_local[b + perm[i]];
+        tv[i] = vals[b + perm[i]];
+      }
+      std::copy(tc.begin(), tc.end(), col_local.begin() + b);
+      std::copy(tv.begin(), tv.end(), vals.begin() + b);
+    }
+    if (ghost) bnd.push_back((int32_t)r);
+  }
+
+  auto* op = new b200_op();
+  op->ctx = ctx;
+  op->n_global = n_global;
+  op->row_begin = rb;
+  op->row_end = re;
+  op->n_local = n_local;
+  op->n_ghost = n_ghost;
+  op->nnz = nnz;
+  op->max_row_nnz = max_row;
+  op->n_bnd = (int64_t)bnd.size();
+  int rc = upload(&op->rowptr, rp);
+  if (!rc) rc = upload(&op->colind, col_local);
+  if (!rc) rc = upload(&op->values, vals);
+  if (!rc) rc = upload(&op->bnd_rows, bnd);
+  if (rc) {
+    b200_op_destroy(op);
+    return rc;
+  }
+
+  if (ctx->nranks > 1) {
+    const int P = ctx->nranks, me = ctx->rank;
+    // recv side: ghosts are sorted by GID, hence grouped by owner
+    std::vector<int64_t> need(P, 0), recv_off(P, 0);
+    for (int64_t g = 0; g < n_ghost; ++g) need[ghost_owner[g]]++;
+    for (int r = 1; r < P; ++r) recv_off[r] = recv_off[r - 1] + need[r - 1];
+    // everyone learns the full P x P "needs" matrix (row = requester)
+    std::vector<int64_t> M((size_t)P * P, 0);
+    for (int r = 0; r < P; ++r) M[(size_t)me * P + r] = need[r];
+    int64_t* dM = nullptr;
+    rc = upload(&dM, M);
+    if (!rc) rc = nccl_allreduce_i64(ctx, dM, (size_t)P * P, ctx->stream);
+    if (!rc && cudaMemcpyAsync(M.data(), dM, sizeof(int64_t) * P * P, cudaMemcpyDeviceToHost,
+                               ctx->stream) != cudaSuccess)
+      rc = fail(B200_ERR_CUDA, "halo setup: D2H copy failed");
+    if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+      rc = fail(B200_ERR_CUDA, "halo setup: sync failed");
+    cudaFree(dM);
+    if (rc) {
+      b200_op_destroy(op);
+      return rc;
+    }
+    std::vector<int64_t> send_cnt(P, 0), send_off(P, 0);
+    for (int r = 0; r < P; ++r) send_cnt[r] = M[(size_t)r * P + me];
+    for (int r = 1; r < P; ++r) send_off[r] = send_off[r - 1] + send_cnt[r - 1];
+    const int64_t n_send = send_off[P - 1] + send_cnt[P - 1];
+    // exchange the GID lists: I tell each owner which of its rows I need
+    int64_t *d_need = nullptr, *d_asked = nullptr;
+    rc = upload(&d_need, ghost_gids);
+    std::vector<int64_t> asked((size_t)n_send, 0);
+    if (!rc) rc = upload(&d_asked, asked);
+    if (!rc) rc = nccl_group_start(ctx);
+    for (int r = 0; r < P && !rc; ++r) {
+      if (need[r] > 0)
+        rc = nccl_send(ctx, d_need + recv_off[r], (size_t)need[r], false, r, ctx->stream);
+      if (!rc && send_cnt[r] > 0)
+        rc = nccl_recv(ctx, d_asked + send_off[r], (size_t)send_cnt[r], false, r, ctx->stream);
+    }
+    if (!rc) rc = nccl_group_end(ctx);
+    if (!rc && n_send > 0 &&
+        cudaMemcpyAsync(asked.data(), d_asked, sizeof(int64_t) * n_send, cudaMemcpyDeviceToHost,
+                        ctx->stream) != cudaSuccess)
+      rc = fail(B200_ERR_CUDA, "halo setup: D2H copy failed");
+    if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+      rc = fail(B200_ERR_CUDA, "halo setup: sync failed");
+    cudaFree(d_need);
+    cudaFree(d_asked);
+    if (rc) {
+      b200_op_destroy(op);
+      return rc;
+    }
+    std::vector<int32_t> send_idx((size_t)n_send);
+    for (int64_t i = 0; i < n_send; ++i) {
+      const int64_t g = asked[i];
+      if (g < rb || g >= re) {
+        b200_op_destroy(op);
+        return fail(B200_ERR_ARG, "halo setup: a peer asked for a row this rank does not own");
+      }
+      send_idx[i] = (int32_t)(g - rb);
+    }
+    op->n_send = n_send;
+    rc = upload(&op->send_idx, send_idx);
+    if (rc) {
+      b200_op_destroy(op);
+      return rc;
+    }
+    for (int r = 0; r < P; ++r)
+      if (need[r] > 0 || send_cnt[r] > 0)
+        op->peers.push_back(HaloPeer{r, send_off[r], send_cnt[r], recv_off[r], need[r]});
+  }
+  *out = op;
+  return 0;
+}
+
+extern "C" int b200_op_destroy(b200_op* op) {
+  if (!op) return 0;
+  cudaFree(op->rowptr);
+  cudaFree(op->colind);
+  cudaFree(op->values);
+  cudaFree(op->bnd_rows);
+  cudaFree(op->int_rows);
+  cudaFree(op->send_idx);
+  cudaFree(op->send_buf);
+  cudaFree(op->recv_buf);
+  cudaFree(op->xcol);
+  delete op;
+  return 0;
+}
+
+extern "C" int b200_op_info(const b200_op* op, int64_t* n_local, int64_t* n_global,
+                            int64_t* nnz_local, int64_t* n_ghost, int64_t* n_boundary_rows) {
+  if (!op) return fail(B200_ERR_ARG, "b200_op_info: null operator");
+  if (n_local) *n_local = op->n_local;
+  if (n_global) *n_global = op->n_global;
+  if (nnz_local) *nnz_local = op->nnz;
+  if (n_ghost) *n_ghost = op->n_ghost;
+  if (n_boundary_rows) *n_boundary_rows = op->n_bnd;
+  return 0;
+}
+
+extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, int trans) {
+  if (!op_c || !x || !y) return fail(B200_ERR_ARG, "Apply: null argument");
+  if (trans != 0)
+    return fail(B200_ERR_UNSUPPORTED, "Apply: transpose apply is not implemented on this path");
+  b200_op* op = const_cast<b200_op*>(op_c);
+  Ctx* ctx = op->ctx;
+  if (x->ncols() != y->ncols())
+    return fail(B200_ERR_ARG, "Apply: x and y have different numbers of vectors (Epetra: -2)");
+  if (x->n_local != op->n_local || y->n_local != op->n_local || x->n_global != op->n_global)
+    return fail(B200_ERR_SHAPE, "Apply: multivector map does not match the operator");
+  const int k = x->ncols();
+  if (k == 0) return 0;
+  // X == Y: Epetra applies into a temporary (Epetra_CrsMatrix.cpp:3152); do the same
+  b200_mv* xtmp = nullptr;
+  if (columns_overlap(x, y)) {
+    B200_TRY(b200_mv_clone_copy(x, nullptr, 0, &xtmp));
+    x = xtmp;
+  }
+  int rc = 0;
+  const double algo_bytes =
+      12.0 * op->nnz + 4.0 * (op->n_local + 1) + 16.0 * (double)op->n_local * k;
+  for (int j = 0; j < k && !rc;) {
+    const int len = run_length(j, k, x, j, y, j);
+    const double* xp = x->col(j);
+    double* yp = y->col(j);
+    if (ctx->nranks == 1 || op->peers.empty()) {
+      ctx->t_begin(K_SPMM, algo_bytes * len / k);
+      rc = launch_spmm(ctx, op, nullptr, 0, xp, x->ld, yp, y->ld, len);
+      ctx->t_end();
+    } else {
+      // grow halo buffers
+      if ((size_t)len > op->buf_k) {
+        cudaStreamSynchronize(ctx->stream);
+        cudaStreamSynchronize(ctx->comm_stream);
+        cudaFree(op->send_buf);
+        cudaFree(op->recv_buf);
+        op->send_buf = op->recv_buf = nullptr;
+        if (cudaMalloc((void**)&op->send_buf,
+                       std::max<size_t>(1, (size_t)op->n_send * len) * 8) != cudaSuccess ||
+            cudaMalloc((void**)&op->recv_buf,
+                       std::max<size_t>(1, (size_t)op->n_ghost * len) * 8) != cudaSuccess) {
+          rc = fail(B200_ERR_CUDA, "Apply: halo buffer allocation failed");
+          break;
+        }
+        op->buf_k = (size_t)len;
+      }
+      // 1. pack the rows my neighbours need (compute stream: x is produced there)
+      ctx->t_begin(K_HALO, 16.0 * (double)op->n_send * len);
+      rc = launch_pack(ctx, ctx->stream, op->send_idx, op->n_send, xp, x->ld, len, op->send_buf);
+      ctx->t_end();
+      if (rc) break;
+      if (cudaEventRecord(ctx->ev_compute, ctx->stream) != cudaSuccess ||
+          cudaStreamWaitEvent(ctx->comm_stream, ctx->ev_compute, 0) != cudaSuccess) {
+        rc = fail(B200_ERR_CUDA, "Apply: event handoff failed");
+        break;
+      }
+      // 2. NCCL send/recv on the comm stream, one slice per (peer, rhs) so the ghost block is
+      //    received directly in its final [rhs][ghost] layout (no unpack kernel)
+      rc = nccl_group_start(ctx);
+      for (size_t pi = 0; pi < op->peers.size() && !rc; ++pi) {
+        const HaloPeer& pr = op->peers[pi];
+        for (int c = 0; c < len && !rc; ++c) {
+          if (pr.send_cnt > 0)
+            rc = nccl_send(ctx, op->send_buf + (size_t)c * op->n_send + pr.send_off,
+                           (size_t)pr.send_cnt, true, pr.rank, ctx->comm_stream);
+          if (!rc && pr.recv_cnt > 0)
+            rc = nccl_recv(ctx, op->recv_buf + (size_t)c * op->n_ghost + pr.recv_off,
+                           (size_t)pr.recv_cnt, true, pr.rank, ctx->comm_stream);
+        }
+      }
+      if (!rc) rc = nccl_group_end(ctx);
+      if (rc) break;
+      ++ctx->launches;
+      cudaEventRecord(ctx->ev_comm, ctx->comm_stream);
+      // 3. interior rows while the halo is in flight
+      ctx->t_begin(K_SPMM, algo_bytes * len / k);
+      rc = launch_spmm(ctx, op, nullptr, -1, xp, x->ld, yp, y->ld, len);
+      if (rc) break;
+      // 4. boundary rows once the ghosts have landed
+      cudaStreamWaitEvent(ctx->stream, ctx->ev_comm, 0);
+      rc = launch_spmm(ctx, op, op->bnd_rows, op->n_bnd, xp, x->ld, yp, y->ld, len);
+      ctx->t_end();
+    }
+    j += len;
+  }
+  if (xtmp) b200_mv_destroy(xtmp);
+  return rc;
+}

@@ -1,0 +1,174 @@
+// Streaming element-wise multivector kernels (MvAddMv, MvScale, MvInit, MvRandom, copies).
+// All are HBM/L2-bandwidth bound: 256-bit loads/stores, one column per blockIdx.y,
+// grid-stride over 4-row vectors.  Columns are 256-byte aligned (ld % 32 == 0), so touching
+// the padding rows [n, round4(n)) of a column is safe and never observable.
+//
+// Reference semantics: Epetra_MultiVector::Update  epetra/src/Epetra_MultiVector.cpp:1276-1500
+//                      Epetra_MultiVector::Scale   :1229-1248, PutScalar :595-608,
+//                      Random :490-515 with Epetra_Util::RandomDouble epetra/src/Epetra_Util.cpp:71-99
+#include "device_utils.cuh"
+#include "runtime.cuh"
+
+namespace b200 {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+inline dim3 ew_grid(int64_t n, int k) {
+  int64_t vecs = (n + 3) / 4;
+  int64_t bx = (vecs + kThreads - 1) / kThreads;
+  // enough CTAs for ~4 waves of 148 SMs x 8 resident CTAs, but no more than needed
+  int64_t cap = std::max<int64_t>(1, (int64_t)kNumSM * 8 * 4 / std::max(1, k));
+  if (bx > cap) bx = cap;
+  if (bx < 1) bx = 1;
+  return dim3((unsigned)bx, (unsigned)k, 1);
+}
+
+__global__ void __launch_bounds__(kThreads) fill_kernel(double* __restrict__ y, int64_t ld,
+                                                         int64_t nvec, double a) {
+  double* yc = y + (size_t)blockIdx.y * ld;
+  const double4v v{a, a, a, a};
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * blockDim.x)
+    st_plain4(yc + 4 * i, v);
+}
+
+// MODE 0: y = alpha*A ; MODE 1: y = alpha*A + beta*B.  A/B may alias y exactly.
+template <int MODE>
+__global__ void __launch_bounds__(kThreads)
+    axpby_kernel(double* y, int64_t ldy, const double* a, int64_t lda, const double* b,
+                 int64_t ldb, int64_t nvec, double alpha, double beta) {
+  double* yc = y + (size_t)blockIdx.y * ldy;
+  const double* ac = a + (size_t)blockIdx.y * lda;
+  const double* bc = (MODE == 1) ? b + (size_t)blockIdx.y * ldb : nullptr;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    double4v va = ld_plain4(ac + 4 * i);
+    double4v r;
+    if (MODE == 0) {
+      r.x = alpha * va.x; r.y = alpha * va.y; r.z = alpha * va.z; r.w = alpha * va.w;
+    } else {
+      double4v vb = ld_plain4(bc + 4 * i);
+      r.x = alpha * va.x + beta * vb.x;
+      r.y = alpha * va.y + beta * vb.y;
+      r.z = alpha * va.z + beta * vb.z;
+      r.w = alpha * va.w + beta * vb.w;
+    }
+    st_plain4(yc + 4 * i, r);
+  }
+}
+
+struct ColScales { double a[32]; };
+
+__global__ void __launch_bounds__(kThreads)
+    scale_cols_kernel(double* y, int64_t ld, int64_t nvec, ColScales s) {
+  double* yc = y + (size_t)blockIdx.y * ld;
+  const double a = s.a[blockIdx.y];
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    double4v v = ld_plain4(yc + 4 * i);
+    v.x *= a; v.y *= a; v.z *= a; v.w *= a;
+    st_plain4(yc + 4 * i, v);
+  }
+}
+
+// Park-Miller minimal standard generator: s <- 16807*s mod (2^31-1); value = 2*(s/m) - 1.
+// Element (global row g, column c) takes the (seq_start + g + c*n_global + 1)-th state after
+// `seed`, so the stream is independent of the row partition and of the launch geometry.
+__device__ __forceinline__ unsigned int pm_mul(unsigned int a, unsigned int b) {
+  return (unsigned int)(((unsigned long long)a * b) % 2147483647ull);
+}
+__device__ unsigned int pm_pow(unsigned long long e) {
+  unsigned int r = 1, base = 16807u;
+  while (e) {
+    if (e & 1ull) r = pm_mul(r, base);
+    base = pm_mul(base, base);
+    e >>= 1;
+  }
+  return r;
+}
+constexpr int kRandChunk = 32;
+__global__ void __launch_bounds__(kThreads)
+    random_kernel(double* y, int64_t ld, int64_t n, int64_t row_offset, int64_t n_global,
+                  int64_t seq_start, unsigned int seed) {
+  double* yc = y + (size_t)blockIdx.y * ld;
+  const int64_t nchunk = (n + kRandChunk - 1) / kRandChunk;
+  for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < nchunk;
+       c += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r0 = c * kRandChunk;
+    const unsigned long long idx =
+        (unsigned long long)seq_start + (unsigned long long)(row_offset + r0) +
+        (unsigned long long)blockIdx.y * (unsigned long long)n_global;
+    unsigned int s = pm_mul(seed % 2147483647u, pm_pow(idx));  // state before element r0
+    const int64_t r1 = min(n, r0 + (int64_t)kRandChunk);
+    for (int64_t r = r0; r < r1; ++r) {
+      s = pm_mul(s, 16807u);
+      yc[r] = 2.0 * ((double)s / 2147483647.0) - 1.0;
+    }
+  }
+}
+
+}  // namespace
+
+int launch_fill(Ctx* ctx, double* y, int64_t ld, int64_t n, int k, double a) {
+  if (n <= 0 || k <= 0) return 0;
+  ctx->t_begin(K_AXPBY, 8.0 * n * k);
+  fill_kernel<<<ew_grid(n, k), kThreads, 0, ctx->stream>>>(y, ld, (n + 3) / 4, a);
+  ctx->t_end();
+  ++ctx->launches;
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_axpby(Ctx* ctx, double* y, int64_t ldy, const double* a, int64_t lda, const double* b,
+                 int64_t ldb, int64_t n, int k, double alpha, double beta) {
+  if (n <= 0 || k <= 0) return 0;
+  const dim3 g = ew_grid(n, k);
+  if (b == nullptr) {
+    ctx->t_begin(K_AXPBY, 16.0 * n * k);
+    axpby_kernel<0><<<g, kThreads, 0, ctx->stream>>>(y, ldy, a, lda, nullptr, 0, (n + 3) / 4,
+                                                      alpha, 0.0);
+  } else {
+    ctx->t_begin(K_AXPBY, 24.0 * n * k);
+    axpby_kernel<1><<<g, kThreads, 0, ctx->stream>>>(y, ldy, a, lda, b, ldb, (n + 3) / 4, alpha,
+                                                      beta);
+  }
+  ctx->t_end();
+  ++ctx->launches;
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_scale_cols(Ctx* ctx, double* y, int64_t ld, int64_t n, int k,
+                      const double* alpha_host) {
+  if (n <= 0) return 0;
+  for (int j0 = 0; j0 < k; j0 += 32) {
+    const int kk = std::min(32, k - j0);
+    ColScales s;
+    for (int j = 0; j < kk; ++j) s.a[j] = alpha_host[j0 + j];
+    ctx->t_begin(K_AXPBY, 16.0 * n * kk);
+    scale_cols_kernel<<<ew_grid(n, kk), kThreads, 0, ctx->stream>>>(y + (size_t)j0 * ld, ld,
+                                                                     (n + 3) / 4, s);
+    ctx->t_end();
+    ++ctx->launches;
+    B200_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+int launch_random(Ctx* ctx, double* y, int64_t ld, int64_t n, int k, int64_t row_offset,
+                  int64_t n_global, int64_t seq_start, unsigned int seed) {
+  if (n <= 0 || k <= 0) return 0;
+  const int64_t nchunk = (n + kRandChunk - 1) / kRandChunk;
+  int64_t bx = std::min<int64_t>((nchunk + kThreads - 1) / kThreads, kNumSM * 8);
+  ctx->t_begin(K_AXPBY, 8.0 * n * k);
+  random_kernel<<<dim3((unsigned)std::max<int64_t>(bx, 1), (unsigned)k), kThreads, 0,
+                  ctx->stream>>>(y, ld, n, row_offset, n_global, seq_start, seed);
+  ctx->t_end();
+  ++ctx->launches;
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace b200

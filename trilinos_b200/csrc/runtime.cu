@@ -1,0 +1,388 @@
+// Context: device selection, streams, caching pool, host mailbox, workspace, NCCL (dlopen),
+// per-kernel-class event timing.  Replaces Epetra_Comm / Epetra_MpiComm for this path
+// (epetra/src/Epetra_MpiComm.cpp:62,126,154; Epetra_SerialComm.cpp:117-152).
+#include "runtime.cuh"
+
+#include <dlfcn.h>
+#include <immintrin.h>
+
+#include <atomic>
+#include <chrono>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace b200 {
+
+static thread_local char g_err[1024] = "";
+
+int fail(int code, const char* msg) {
+  std::snprintf(g_err, sizeof(g_err), "%s", msg);
+  return code;
+}
+int failf(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  std::vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+// ------------------------------------------------------------------ NCCL via dlopen
+// The single-GPU path must not depend on libnccl being loadable; the multi-rank path resolves
+// the handful of entry points it needs at b200_ctx_comm_init time.
+struct Id128 { char b[128]; };
+struct NcclApi {
+  void* h = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, /*ncclUniqueId by value*/ Id128, int) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*Send)(const void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+constexpr int kNcclFloat64 = 8, kNcclInt64 = 4, kNcclSum = 0, kNcclMax = 2;
+
+static NcclApi* load_nccl() {
+  static NcclApi api;
+  if (api.h) return &api;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* nm : names) {
+    api.h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+    if (api.h) break;
+  }
+  if (!api.h) return nullptr;
+#define B200_SYM(field, name)                                                 \
+  *(void**)(&api.field) = dlsym(api.h, name);                                 \
+  if (!api.field) {                                                           \
+    api.h = nullptr;                                                          \
+    return nullptr;                                                           \
+  }
+  B200_SYM(GetUniqueId, "ncclGetUniqueId");
+  B200_SYM(CommInitRank, "ncclCommInitRank");
+  B200_SYM(CommDestroy, "ncclCommDestroy");
+  B200_SYM(AllReduce, "ncclAllReduce");
+  B200_SYM(Send, "ncclSend");
+  B200_SYM(Recv, "ncclRecv");
+  B200_SYM(GroupStart, "ncclGroupStart");
+  B200_SYM(GroupEnd, "ncclGroupEnd");
+  B200_SYM(GetErrorString, "ncclGetErrorString");
+#undef B200_SYM
+  return &api;
+}
+
+#define B200_NCCL(api, call)                                                              \
+  do {                                                                                    \
+    int r_ = (call);                                                                      \
+    if (r_ != 0)                                                                          \
+      return ::b200::failf(B200_ERR_NCCL, "%s:%d NCCL: %s", __FILE__, __LINE__,           \
+                           (api)->GetErrorString(r_));                                    \
+  } while (0)
+
+// helpers used by capi.cu for the halo exchange / setup exchange
+int nccl_allreduce_f64(Ctx* ctx, double* buf, size_t count, bool is_max, cudaStream_t s) {
+  B200_NCCL(ctx->nccl, ctx->nccl->AllReduce(buf, buf, count, kNcclFloat64,
+                                            is_max ? kNcclMax : kNcclSum, ctx->comm, s));
+  return 0;
+}
+int nccl_allreduce_i64(Ctx* ctx, int64_t* buf, size_t count, cudaStream_t s) {
+  B200_NCCL(ctx->nccl,
+            ctx->nccl->AllReduce(buf, buf, count, kNcclInt64, kNcclSum, ctx->comm, s));
+  return 0;
+}
+int nccl_group_start(Ctx* ctx) {
+  B200_NCCL(ctx->nccl, ctx->nccl->GroupStart());
+  return 0;
+}
+int nccl_group_end(Ctx* ctx) {
+  B200_NCCL(ctx->nccl, ctx->nccl->GroupEnd());
+  return 0;
+}
+int nccl_send(Ctx* ctx, const void* buf, size_t count, bool f64, int peer, cudaStream_t s) {
+  B200_NCCL(ctx->nccl,
+            ctx->nccl->Send(buf, count, f64 ? kNcclFloat64 : kNcclInt64, peer, ctx->comm, s));
+  return 0;
+}
+int nccl_recv(Ctx* ctx, void* buf, size_t count, bool f64, int peer, cudaStream_t s) {
+  B200_NCCL(ctx->nccl,
+            ctx->nccl->Recv(buf, count, f64 ? kNcclFloat64 : kNcclInt64, peer, ctx->comm, s));
+  return 0;
+}
+
+// ------------------------------------------------------------------ pool
+int Ctx::alloc(size_t bytes, void** out) {
+  bytes = (bytes + 511) & ~(size_t)511;
+  if (bytes == 0) bytes = 512;
+  auto it = pool.find(bytes);
+  if (it != pool.end()) {
+    *out = it->second;
+    pool.erase(it);
+    pool_bytes -= bytes;
+    return 0;
+  }
+  cudaError_t e = cudaMalloc(out, bytes);
+  if (e != cudaSuccess) {
+    // drop the cache and retry once
+    for (auto& kv : pool) cudaFree(kv.second);
+    pool.clear();
+    pool_bytes = 0;
+    cudaGetLastError();
+    e = cudaMalloc(out, bytes);
+  }
+  if (e != cudaSuccess)
+    return failf(B200_ERR_CUDA, "cudaMalloc(%zu bytes): %s", bytes, cudaGetErrorString(e));
+  return 0;
+}
+
+void Ctx::release(void* p, size_t bytes) {
+  if (!p) return;
+  bytes = (bytes + 511) & ~(size_t)511;
+  if (bytes == 0) bytes = 512;
+  // Stream-ordered reuse: every kernel of this context runs on `stream`, so a block handed
+  // out again is only touched after all previously enqueued work on it.
+  pool.emplace(bytes, p);
+  pool_bytes += bytes;
+}
+
+// ------------------------------------------------------------------ timing
+void Ctx::t_begin(int cls, double bytes) {
+  if (!timing) return;
+  Stamp s;
+  auto get = [&]() {
+    cudaEvent_t e;
+    if (!ev_free.empty()) {
+      e = ev_free.back();
+      ev_free.pop_back();
+    } else {
+      cudaEventCreate(&e);
+    }
+    return e;
+  };
+  s.a = get();
+  s.b = get();
+  s.cls = cls;
+  cudaEventRecord(s.a, stream);
+  stamps.push_back(s);
+  t_calls[cls] += 1;
+  t_bytes[cls] += bytes;
+}
+void Ctx::t_end() {
+  if (!timing || stamps.empty()) return;
+  cudaEventRecord(stamps.back().b, stream);
+  if (stamps.size() >= 4096) t_drain();
+}
+int Ctx::t_drain() {
+  if (stamps.empty()) return 0;
+  B200_CUDA(cudaStreamSynchronize(stream));
+  for (auto& s : stamps) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, s.a, s.b);
+    t_ms[s.cls] += ms;
+    ev_free.push_back(s.a);
+    ev_free.push_back(s.b);
+  }
+  stamps.clear();
+  return 0;
+}
+
+// ------------------------------------------------------------------ mailbox
+int Ctx::wait_flag(uint64_t s) {
+  ++syncs;
+  using clk = std::chrono::steady_clock;
+  const auto t0 = clk::now();
+  uint64_t spins = 0;
+  while (true) {
+    if (*flag_h >= s) break;
+    _mm_pause();
+    if ((++spins & 0xfffff) == 0) {
+      cudaError_t e = cudaStreamQuery(stream);
+      if (e != cudaSuccess && e != cudaErrorNotReady)
+        return failf(B200_ERR_CUDA, "device error while waiting for a reduction: %s",
+                     cudaGetErrorString(e));
+      if (e == cudaSuccess && *flag_h < s) {
+        // stream drained but the flag never arrived: should be impossible
+        _mm_pause();
+        if (*flag_h < s) return fail(B200_ERR_CUDA, "reduction result was never published");
+      }
+      if (std::chrono::duration<double>(clk::now() - t0).count() > 120.0)
+        return fail(B200_ERR_TIMEOUT, "timeout waiting for a reduction result");
+    }
+  }
+  std::atomic_thread_fence(std::memory_order_acquire);
+  return 0;
+}
+
+int Ctx::finish_reduction(int count, bool is_max) {
+  if (nranks > 1) {
+    B200_TRY(nccl_allreduce_f64(this, red_d, (size_t)count, is_max, stream));
+    ++launches;
+    B200_TRY(launch_publish(this, count));
+  }
+  return wait_flag(seq);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" const char* b200_last_error(void) { return g_err; }
+extern "C" const char* b200_version(void) { return "trilinos_b200 0.1 (sm_100a)"; }
+
+extern "C" int b200_ctx_create(int device, b200_ctx** out) {
+  if (!out) return fail(B200_ERR_ARG, "b200_ctx_create: null out");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return fail(B200_ERR_NO_DEVICE,
+                "no CUDA device: the B200 path has no CPU fallback (cudaGetDeviceCount failed)");
+  }
+  if (device < 0 || device >= ndev) return fail(B200_ERR_ARG, "b200_ctx_create: bad device id");
+  B200_CUDA(cudaSetDevice(device));
+  auto* c = new b200_ctx();
+  c->device = device;
+  B200_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  B200_CUDA(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+  B200_CUDA(cudaEventCreateWithFlags(&c->ev_comm, cudaEventDisableTiming));
+  B200_CUDA(cudaEventCreateWithFlags(&c->ev_compute, cudaEventDisableTiming));
+  void* hp = nullptr;
+  B200_CUDA(cudaHostAlloc(&hp, kMailboxDoubles * sizeof(double) + 64, cudaHostAllocMapped));
+  std::memset(hp, 0, kMailboxDoubles * sizeof(double) + 64);
+  c->flag_h = (volatile uint64_t*)hp;
+  c->mbox_h = (double*)((char*)hp + 64);
+  void* dp = nullptr;
+  B200_CUDA(cudaHostGetDevicePointer(&dp, hp, 0));
+  c->flag_d = (uint64_t*)dp;
+  c->mbox_d = (double*)((char*)dp + 64);
+  B200_CUDA(cudaMalloc((void**)&c->ws, kWorkspaceBytes));
+  B200_CUDA(cudaMalloc((void**)&c->ticket, 256));
+  B200_CUDA(cudaMemset(c->ticket, 0, 256));
+  B200_CUDA(cudaMalloc((void**)&c->red_d, kMailboxDoubles * sizeof(double)));
+  B200_CUDA(cudaMalloc((void**)&c->dB, kStageSlotBytes));
+  B200_CUDA(cudaHostAlloc((void**)&c->stage_h, kStageSlots * kStageSlotBytes, cudaHostAllocDefault));
+  for (int i = 0; i < kStageSlots; ++i)
+    B200_CUDA(cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming));
+  B200_CUDA(cudaDeviceSynchronize());
+  *out = c;
+  return 0;
+}
+
+extern "C" int b200_ctx_destroy(b200_ctx* c) {
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  if (c->comm && c->nccl) c->nccl->CommDestroy(c->comm);
+  for (auto& kv : c->pool) cudaFree(kv.second);
+  c->pool.clear();
+  for (auto& s : c->stamps) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
+  for (auto e : c->ev_free) cudaEventDestroy(e);
+  for (int i = 0; i < kStageSlots; ++i) cudaEventDestroy(c->stage_ev[i]);
+  cudaFreeHost((void*)c->flag_h);
+  cudaFreeHost(c->stage_h);
+  cudaFree(c->ws);
+  cudaFree(c->ticket);
+  cudaFree(c->red_d);
+  cudaFree(c->dB);
+  if (c->flush_buf) cudaFree(c->flush_buf);
+  cudaEventDestroy(c->ev_comm);
+  cudaEventDestroy(c->ev_compute);
+  cudaStreamDestroy(c->stream);
+  cudaStreamDestroy(c->comm_stream);
+  delete c;
+  return 0;
+}
+
+extern "C" int b200_ctx_sync(b200_ctx* c) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  B200_CUDA(cudaStreamSynchronize(c->stream));
+  B200_CUDA(cudaStreamSynchronize(c->comm_stream));
+  return 0;
+}
+
+extern "C" int b200_comm_unique_id(void* id128) {
+  NcclApi* api = load_nccl();
+  if (!api) return fail(B200_ERR_NCCL, "libnccl.so.2 could not be loaded");
+  B200_NCCL(api, api->GetUniqueId(id128));
+  return 0;
+}
+
+extern "C" int b200_ctx_comm_init(b200_ctx* c, const void* id128, int nranks, int rank) {
+  if (!c || !id128 || nranks < 1 || rank < 0 || rank >= nranks)
+    return fail(B200_ERR_ARG, "b200_ctx_comm_init: bad arguments");
+  if (nranks == 1) {
+    c->rank = 0;
+    c->nranks = 1;
+    return 0;
+  }
+  NcclApi* api = load_nccl();
+  if (!api) return fail(B200_ERR_NCCL, "libnccl.so.2 could not be loaded");
+  B200_CUDA(cudaSetDevice(c->device));
+  Id128 id;
+  std::memcpy(id.b, id128, 128);
+  void* comm = nullptr;
+  B200_NCCL(api, api->CommInitRank(&comm, nranks, id, rank));
+  c->nccl = api;
+  c->comm = comm;
+  c->rank = rank;
+  c->nranks = nranks;
+  return 0;
+}
+
+extern "C" int b200_ctx_rank(const b200_ctx* c, int* rank, int* nranks) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  if (rank) *rank = c->rank;
+  if (nranks) *nranks = c->nranks;
+  return 0;
+}
+
+extern "C" int b200_ctx_set_seed(b200_ctx* c, unsigned int seed) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  seed %= 2147483647u;
+  if (seed == 0) seed = 1;
+  c->seed = seed;
+  return 0;
+}
+
+extern "C" int b200_ctx_counters(const b200_ctx* c, int64_t* launches, int64_t* syncs) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  if (launches) *launches = c->launches;
+  if (syncs) *syncs = c->syncs;
+  return 0;
+}
+
+extern "C" int b200_ctx_timing_enable(b200_ctx* c, int on) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  if (!on) B200_TRY(c->t_drain());
+  c->timing = on != 0;
+  return 0;
+}
+
+extern "C" int b200_ctx_timing_read(b200_ctx* c, double* ms, int64_t* calls, double* bytes,
+                                    int reset) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  B200_TRY(c->t_drain());
+  for (int i = 0; i < B200_NUM_KCLASS; ++i) {
+    if (ms) ms[i] = c->t_ms[i];
+    if (calls) calls[i] = c->t_calls[i];
+    if (bytes) bytes[i] = c->t_bytes[i];
+    if (reset) {
+      c->t_ms[i] = 0;
+      c->t_calls[i] = 0;
+      c->t_bytes[i] = 0;
+    }
+  }
+  return 0;
+}
+
+extern "C" void* b200_ctx_stream(b200_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+extern "C" int b200_ctx_flush_l2(b200_ctx* c) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  const size_t bytes = 256u << 20;  // 2 x the 126 MB L2
+  if (!c->flush_buf) B200_CUDA(cudaMalloc(&c->flush_buf, bytes));
+  B200_CUDA(cudaMemsetAsync(c->flush_buf, 0, bytes, c->stream));
+  return 0;
+}

@@ -1,0 +1,194 @@
+// Device runtime of the B200 Block GMRES path: context (streams, memory pool,
+// host mailbox, partial-sum workspace, NCCL), multivector and operator objects.
+#ifndef B200_RUNTIME_CUH
+#define B200_RUNTIME_CUH
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <vector>
+
+#include "b200_belos.h"
+#include "internal.h"
+
+namespace b200 {
+
+constexpr int kNumSM = 148;            // B200: 2 dies x 74 SMs
+constexpr int kLdAlign = 32;           // leading dimension padded to 32 doubles (256 B)
+constexpr size_t kMailboxDoubles = 1u << 16;   // 512 KB host-mapped result mailbox
+constexpr size_t kWorkspaceBytes = 256u << 20; // per-CTA partial sums
+constexpr int kStageSlots = 16;
+constexpr size_t kStageSlotBytes = 512u << 10; // host B blocks for MvTimesMatAddMv
+
+#define B200_CUDA(call)                                                                   \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      return ::b200::failf(B200_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call,      \
+                           cudaGetErrorString(e_));                                       \
+  } while (0)
+
+#define B200_TRY(call)            \
+  do {                            \
+    int rc_ = (call);             \
+    if (rc_ != 0) return rc_;     \
+  } while (0)
+
+struct NcclApi;  // dlopen'ed function table (runtime.cu)
+
+enum KClass { K_SPMM = 0, K_GRAM = 1, K_UPDATE = 2, K_REDUCE = 3, K_AXPBY = 4, K_HALO = 5 };
+
+struct Ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;       // compute stream (all kernels)
+  cudaStream_t comm_stream = nullptr;  // halo exchange
+  cudaEvent_t ev_comm = nullptr, ev_compute = nullptr;
+  // size-bucketed caching pool: Clone/CloneCopy are called several times per Arnoldi step
+  std::multimap<size_t, void*> pool;
+  size_t pool_bytes = 0;
+  // host-mapped mailbox for reduction results + completion flag
+  double* mbox_h = nullptr;
+  double* mbox_d = nullptr;
+  volatile uint64_t* flag_h = nullptr;
+  uint64_t* flag_d = nullptr;
+  uint64_t seq = 0;
+  // device scratch
+  double* ws = nullptr;            // per-CTA partials
+  unsigned int* ticket = nullptr;  // last-block election counter (self-resetting)
+  double* red_d = nullptr;         // device-side result (multi-rank: allreduce in place)
+  double* dB = nullptr;            // device copy of the host dense block B
+  char* stage_h = nullptr;         // pinned staging ring for B
+  cudaEvent_t stage_ev[kStageSlots] = {};
+  bool stage_used[kStageSlots] = {};
+  int stage_next = 0;
+  void* flush_buf = nullptr;       // > L2 scratch for bench hygiene
+  // NCCL
+  NcclApi* nccl = nullptr;
+  void* comm = nullptr;
+  int rank = 0, nranks = 1;
+  // Park-Miller state for MvRandom
+  unsigned int seed = 1;
+  // counters / timing
+  int64_t launches = 0, syncs = 0;
+  bool timing = false;
+  struct Stamp { cudaEvent_t a, b; int cls; };
+  std::vector<Stamp> stamps;
+  std::vector<cudaEvent_t> ev_free;
+  double t_ms[B200_NUM_KCLASS] = {};
+  int64_t t_calls[B200_NUM_KCLASS] = {};
+  double t_bytes[B200_NUM_KCLASS] = {};
+
+  int alloc(size_t bytes, void** out);
+  void release(void* p, size_t bytes);
+  // begin/end a timed region for kernel class cls (no-op unless timing enabled)
+  void t_begin(int cls, double bytes);
+  void t_end();
+  int t_drain();
+  // wait until the device has published sequence number `s` into the flag
+  int wait_flag(uint64_t s);
+  // multi-rank: allreduce red_d[0..count) (sum or max) then publish to mailbox; single-rank:
+  // the kernel already wrote the mailbox.  Returns after the host can read mbox_h.
+  int finish_reduction(int count, bool is_max);
+  double* result_ptr() { return nranks > 1 ? red_d : mbox_d; }
+  uint64_t* result_flag() { return nranks > 1 ? nullptr : flag_d; }
+};
+
+struct Storage {
+  Ctx* ctx;
+  double* ptr;
+  size_t bytes;
+  Storage(Ctx* c, double* p, size_t b) : ctx(c), ptr(p), bytes(b) {}
+  ~Storage() { ctx->release(ptr, bytes); }
+};
+
+struct MV {
+  Ctx* ctx;
+  std::shared_ptr<Storage> st;
+  int64_t n_local, n_global, row_offset, ld;
+  std::vector<int> cols;  // column index (inside the storage) of each vector of this object
+  int ncols() const { return (int)cols.size(); }
+  double* col(int j) const { return st->ptr + (size_t)cols[j] * ld; }
+  const int* colv() const { return cols.data(); }
+};
+
+// maximal run [j, j+len) on which every listed multivector advances by exactly one
+// storage column per step (so the run is a plain strided block in each of them)
+inline int run_length(int j, int n, const MV* a, int ja, const MV* b = nullptr, int jb = 0,
+                      const MV* c = nullptr, int jc = 0) {
+  int len = 1;
+  while (j + len < n) {
+    if (a && a->cols[ja + len] != a->cols[ja + len - 1] + 1) break;
+    if (b && b->cols[jb + len] != b->cols[jb + len - 1] + 1) break;
+    if (c && c->cols[jc + len] != c->cols[jc + len - 1] + 1) break;
+    ++len;
+  }
+  return len;
+}
+
+struct HaloPeer {
+  int rank;
+  int64_t send_off, send_cnt;  // rows of mine the peer needs (offset into send_idx)
+  int64_t recv_off, recv_cnt;  // ghost rows I get from the peer (offset into ghost tail)
+};
+
+struct Op {
+  Ctx* ctx;
+  int64_t n_global, row_begin, row_end, n_local, n_ghost, nnz;
+  int32_t* rowptr = nullptr;  // n_local+1
+  int32_t* colind = nullptr;  // local column ids (owned first, then ghosts)
+  double* values = nullptr;
+  // interior / boundary split (boundary rows reference at least one ghost column)
+  int32_t* bnd_rows = nullptr;
+  int64_t n_bnd = 0;
+  int32_t* int_rows = nullptr;  // only when n_ghost > 0
+  int64_t n_int = 0;
+  // halo
+  std::vector<HaloPeer> peers;
+  int32_t* send_idx = nullptr;  // local row ids to pack, grouped by peer
+  int64_t n_send = 0;
+  double* send_buf = nullptr;   // n_send x k  (layout [rhs][row] per peer)
+  double* xcol = nullptr;       // (n_local + n_ghost) x k column-map copy of x (multi-rank)
+  int64_t xcol_ld = 0;
+  int xcol_k = 0;
+  double* recv_buf = nullptr;
+  size_t buf_k = 0;
+  int max_row_nnz = 0;
+};
+
+// ---- kernel launchers (defined in the .cu files) ---------------------------------
+// elementwise.cu
+int launch_fill(Ctx*, double* y, int64_t ld, int64_t n, int k, double a);
+int launch_axpby(Ctx*, double* y, int64_t ldy, const double* a, int64_t lda, const double* b,
+                 int64_t ldb, int64_t n, int k, double alpha, double beta);
+int launch_scale_cols(Ctx*, double* y, int64_t ld, int64_t n, int k, const double* alpha_host);
+int launch_random(Ctx*, double* y, int64_t ld, int64_t n, int k, int64_t row_offset,
+                  int64_t n_global, int64_t seq_start, unsigned int seed);
+// reduce.cu : out[j] for j<k written to ctx->result_ptr()+out_off
+int launch_dot(Ctx*, const double* a, int64_t lda, const double* b, int64_t ldb, int64_t n, int k,
+               int out_off, bool last);
+int launch_norm(Ctx*, const double* a, int64_t lda, int64_t n, int k, int type, int out_off,
+                bool last);
+// gram.cu : C(p x q, ld=ldc) = alpha * A^T V into result_ptr()+out_off
+int launch_gram(Ctx*, const double* A, int64_t lda, int p, const double* V, int64_t ldv, int q,
+                int64_t n, double alpha, int out_off, int ldc, bool last);
+// update.cu : V = alpha*A*B + beta*V with B (p x q, ld = p) already in ctx->dB + boff
+int launch_update(Ctx*, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
+                  int64_t n, const double* dB, int ldb, double alpha, double beta);
+// spmm.cu
+int launch_spmm(Ctx*, const Op* op, const int32_t* rows, int64_t nrows, const double* x,
+                int64_t ldx, double* y, int64_t ldy, int k);
+int launch_pack(Ctx*, cudaStream_t s, const int32_t* idx, int64_t cnt, const double* x,
+                int64_t ldx, int k, double* buf);
+
+// the mailbox publish kernel used after a multi-rank allreduce
+int launch_publish(Ctx*, int count);
+
+}  // namespace b200
+
+struct b200_ctx : b200::Ctx {};
+struct b200_mv : b200::MV {};
+struct b200_op : b200::Op {};
+
+#endif
