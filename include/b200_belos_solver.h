@@ -1,0 +1,62 @@
+/*
+ * b200_belos_solver.h — C entry points of libb200belos_solver.so: the UNMODIFIED
+ * Belos::BlockGmresSolMgr<double, Belos::MultiVec<double>, Belos::Operator<double>>
+ * (belos/src/BelosBlockGmresSolMgr.hpp:916-1303, compiled from the reference headers where
+ * they lie) driving the B200 plugin classes of include/B200BelosAdapter.hpp.
+ *
+ * b200_belos_block_gmres_solve replaces the body of the reference driver
+ * belos/epetra/example/BlockGmres/BlockGmresEpetraGaleriEx.cpp:170-262 (ParameterList,
+ * LinearProblem::setProblem, BlockGmresSolMgr::solve, true-residual check);
+ * b200_belos_mvop_test replaces belos/epetra/test/MVOPTester/cxx_main.cpp:91-176
+ * (Belos::TestMultiVecTraits / TestOperatorTraits, belos/src/BelosMVOPTester.hpp).
+ */
+#ifndef B200_BELOS_SOLVER_H
+#define B200_BELOS_SOLVER_H
+
+#include "b200_belos.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct {
+  int block_size;          /* "Block Size"            (default 1)   */
+  int num_blocks;          /* "Num Blocks"            (default 300) */
+  int max_iters;           /* "Maximum Iterations"    (-1: n/block_size - 1 as the example driver) */
+  int max_restarts;        /* "Maximum Restarts"      (default 20)  */
+  double tol;              /* "Convergence Tolerance" (default 1e-8) */
+  const char* ortho;       /* "Orthogonalization": "DGKS" | "ICGS" | "IMGS" */
+  int verbosity;           /* Belos::MsgType bitmask; 0 = Errors only */
+  int output_frequency;    /* "Output Frequency" (-1: never) */
+  int adaptive_block_size; /* "Adaptive Block Size" (default 1) */
+  int flexible;            /* "Flexible Gmres" (default 0) */
+  int show_timers;         /* print the Teuchos::TimeMonitor summary after the solve */
+} b200_gmres_params;
+
+typedef struct {
+  int converged;           /* Belos::Converged == 1 */
+  int num_iters;           /* BlockGmresSolMgr::getNumIters() */
+  double achieved_tol;     /* BlockGmresSolMgr::achievedTol() */
+  int loss_of_accuracy;    /* BlockGmresSolMgr::isLOADetected() */
+  double solve_seconds;    /* wall time of solve() (host clock) */
+  int num_rhs;
+  double true_rel_resid[64]; /* ||B - A X||_2 / ||B||_2 per right-hand side (first 64) */
+} b200_gmres_result;
+
+void b200_gmres_default_params(b200_gmres_params* p);
+
+/* X (initial guess in, solution out) and B are n x numrhs multivectors of the operator's map. */
+int b200_belos_block_gmres_solve(b200_op* A, b200_mv* X, b200_mv* B, const b200_gmres_params* p,
+                                 b200_gmres_result* r);
+
+/* Runs Belos::TestMultiVecTraits and Belos::TestOperatorTraits (the reference's contract test)
+ * on a B200MultiVec of n rows x ncols columns and a tridiagonal B200CrsOp. 0 = passed. */
+int b200_belos_mvop_test(b200_ctx* ctx, int n, int ncols, int verbose);
+
+/* Timer table of the last solve (Teuchos::TimeMonitor::summarize) written into buf. */
+int b200_belos_timer_summary(char* buf, int buflen);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

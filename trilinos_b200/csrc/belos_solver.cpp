@@ -1,0 +1,158 @@
+// libb200belos_solver.so: unmodified Belos::BlockGmresSolMgr on the B200 plugin classes.
+// See include/b200_belos_solver.h for the reference code each entry point replaces.
+#include "b200_belos_solver.h"
+
+#include <chrono>
+#include <cstring>
+#include <iostream>
+#include <sstream>
+
+#include "B200BelosAdapter.hpp"
+#include "BelosBlockGmresSolMgr.hpp"
+#include "BelosLinearProblem.hpp"
+#include "BelosMVOPTester.hpp"
+#include "BelosOutputManager.hpp"
+#include "Teuchos_ParameterList.hpp"
+#include "Teuchos_RCP.hpp"
+#include "Teuchos_TimeMonitor.hpp"
+
+namespace b200 {
+int fail(int code, const char* msg);
+}
+
+typedef double ST;
+typedef Belos::MultiVec<ST> MV;
+typedef Belos::Operator<ST> OP;
+typedef Belos::MultiVecTraits<ST, MV> MVT;
+typedef Belos::OperatorTraits<ST, MV, OP> OPT;
+
+extern "C" void b200_gmres_default_params(b200_gmres_params* p) {
+  if (!p) return;
+  p->block_size = 1;
+  p->num_blocks = 300;
+  p->max_iters = 1000;
+  p->max_restarts = 20;
+  p->tol = 1e-8;
+  p->ortho = "DGKS";
+  p->verbosity = 0;
+  p->output_frequency = -1;
+  p->adaptive_block_size = 1;
+  p->flexible = 0;
+  p->show_timers = 0;
+}
+
+extern "C" int b200_belos_block_gmres_solve(b200_op* A_h, b200_mv* X_h, b200_mv* B_h,
+                                            const b200_gmres_params* p, b200_gmres_result* r) {
+  using Teuchos::RCP;
+  using Teuchos::rcp;
+  if (!A_h || !X_h || !B_h || !p || !r) return b200::fail(B200_ERR_ARG, "solve: null argument");
+  std::memset(r, 0, sizeof(*r));
+  try {
+    // Non-owning views of the caller's handles: CloneView over all columns shares storage.
+    const int numrhs = b200_mv_num_vecs(B_h);
+    std::vector<int> all(numrhs);
+    for (int i = 0; i < numrhs; ++i) all[i] = i;
+    b200_mv *xv = nullptr, *bv = nullptr;
+    if (b200_mv_clone_view(X_h, all.data(), numrhs, &xv) != 0) return B200_ERR_ARG;
+    if (b200_mv_clone_view(B_h, all.data(), numrhs, &bv) != 0) {
+      b200_mv_destroy(xv);
+      return B200_ERR_ARG;
+    }
+    RCP<MV> X = rcp(new Belos::B200MultiVec(xv));
+    RCP<MV> B = rcp(new Belos::B200MultiVec(bv));
+    RCP<OP> A = rcp(new Belos::B200CrsOp(A_h, false));
+
+    const ptrdiff_t n_global = MVT::GetGlobalLength(*B);
+    int maxiters = p->max_iters;
+    if (maxiters == -1) maxiters = (int)(n_global / std::max(1, p->block_size)) - 1;
+
+    Teuchos::ParameterList belosList;
+    belosList.set("Num Blocks", p->num_blocks);
+    belosList.set("Block Size", p->block_size);
+    belosList.set("Maximum Iterations", maxiters);
+    belosList.set("Maximum Restarts", p->max_restarts);
+    belosList.set("Convergence Tolerance", p->tol);
+    belosList.set("Orthogonalization", std::string(p->ortho ? p->ortho : "DGKS"));
+    belosList.set("Adaptive Block Size", p->adaptive_block_size != 0);
+    if (p->flexible) belosList.set("Flexible Gmres", true);
+    int verbosity = Belos::Errors + Belos::Warnings + p->verbosity;
+    if (p->show_timers) verbosity |= Belos::TimingDetails;
+    belosList.set("Verbosity", verbosity);
+    if (p->output_frequency > 0) belosList.set("Output Frequency", p->output_frequency);
+
+    Belos::LinearProblem<ST, MV, OP> problem(A, X, B);
+    if (!problem.setProblem())
+      return b200::fail(B200_ERR_ARG, "Belos::LinearProblem failed to set up correctly");
+
+    Teuchos::TimeMonitor::zeroOutTimers();
+    Belos::BlockGmresSolMgr<ST, MV, OP> solver(rcp(&problem, false), rcp(&belosList, false));
+    b200_ctx_sync(b200_mv_ctx(B_h));
+    const auto t0 = std::chrono::steady_clock::now();
+    const Belos::ReturnType ret = solver.solve();
+    b200_ctx_sync(b200_mv_ctx(B_h));
+    const auto t1 = std::chrono::steady_clock::now();
+
+    r->converged = (ret == Belos::Converged) ? 1 : 0;
+    r->num_iters = solver.getNumIters();
+    r->achieved_tol = solver.achievedTol();
+    r->loss_of_accuracy = solver.isLOADetected() ? 1 : 0;
+    r->solve_seconds = std::chrono::duration<double>(t1 - t0).count();
+    r->num_rhs = numrhs;
+
+    // true residual check, as the reference driver does after solve()
+    std::vector<double> actual(numrhs), rhs(numrhs);
+    RCP<MV> resid = MVT::Clone(*B, numrhs);
+    OPT::Apply(*A, *X, *resid);
+    MVT::MvAddMv(-1.0, *resid, 1.0, *B, *resid);
+    MVT::MvNorm(*resid, actual);
+    MVT::MvNorm(*B, rhs);
+    for (int i = 0; i < numrhs && i < 64; ++i)
+      r->true_rel_resid[i] = rhs[i] > 0 ? actual[i] / rhs[i] : actual[i];
+    return 0;
+  } catch (const std::exception& e) {
+    return b200::fail(B200_ERR_ARG, e.what());
+  }
+}
+
+extern "C" int b200_belos_timer_summary(char* buf, int buflen) {
+  if (!buf || buflen <= 0) return B200_ERR_ARG;
+  std::ostringstream os;
+  Teuchos::TimeMonitor::summarize(os);
+  const std::string s = os.str();
+  std::strncpy(buf, s.c_str(), (size_t)buflen - 1);
+  buf[buflen - 1] = 0;
+  return 0;
+}
+
+extern "C" int b200_belos_mvop_test(b200_ctx* ctx, int n, int ncols, int verbose) {
+  using Teuchos::RCP;
+  using Teuchos::rcp;
+  if (!ctx || n <= 0 || ncols <= 0) return b200::fail(B200_ERR_ARG, "mvop_test: bad arguments");
+  try {
+    RCP<Belos::OutputManager<ST> > om = rcp(new Belos::OutputManager<ST>());
+    if (verbose) om->setVerbosity(Belos::Warnings + Belos::Errors + Belos::Debug);
+    // tridiagonal operator, as belos/epetra/test/MVOPTester/cxx_main.cpp:112-148
+    int rank = 0, nranks = 1;
+    b200_ctx_rank(ctx, &rank, &nranks);
+    int64_t rb, re;
+    b200_linear_partition(n, nranks, rank, &rb, &re);
+    int64_t nnz = 0;
+    b200_galeri_generate("Tridiag", n, 1, 1, 0, 0, rb, re, &nnz, nullptr, nullptr, nullptr);
+    std::vector<int32_t> rp(re - rb + 1);
+    std::vector<int64_t> ci(nnz);
+    std::vector<double> va(nnz);
+    b200_galeri_generate("Tridiag", n, 1, 1, 0, 0, rb, re, &nnz, rp.data(), ci.data(), va.data());
+    b200_op* op_h = nullptr;
+    if (b200_op_create_csr(ctx, n, rb, re, rp.data(), ci.data(), va.data(), &op_h) != 0) return B200_ERR_ARG;
+    RCP<OP> op = rcp(new Belos::B200CrsOp(op_h, true));
+    RCP<MV> ivec = rcp(new Belos::B200MultiVec(ctx, re - rb, n, rb, ncols));
+    MVT::MvRandom(*ivec);
+    bool ok = Belos::TestMultiVecTraits<ST, MV>(om, ivec);
+    if (!ok) return b200::fail(1, "Belos::TestMultiVecTraits() returned false");
+    ok = Belos::TestOperatorTraits<ST, MV, OP>(om, ivec, op);
+    if (!ok) return b200::fail(2, "Belos::TestOperatorTraits() returned false");
+    return 0;
+  } catch (const std::exception& e) {
+    return b200::fail(B200_ERR_ARG, e.what());
+  }
+}

@@ -57,10 +57,12 @@ __device__ __forceinline__ double warp_max(double v) {
   return v;
 }
 
-// Publish: every thread that wrote host-visible results fences at system scope, the CTA
-// synchronises, then one thread stores the sequence number the host is spinning on.
+// Publish protocol for host-visible results: a thread that stored results into the mapped
+// mailbox calls fence_results() (system-scope fence, ~3 us if a whole CTA does it, so only
+// the writers do), the CTA synchronises, then one thread releases the sequence number the
+// host is spinning on.
+__device__ __forceinline__ void fence_results() { __threadfence_system(); }
 __device__ __forceinline__ void publish_flag(uint64_t* flag, uint64_t seq) {
-  __threadfence_system();
   __syncthreads();
   if (flag != nullptr && threadIdx.x == 0) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(seq) : "memory");

@@ -120,6 +120,7 @@ __global__ void __launch_bounds__(kThreads, 2)
     if (lane == 0) {
       const int k = e / p, col = e % p;
       out[(size_t)k * ldc + col] = alpha * s;
+      fence_results();
     }
   }
   publish_flag(flag, seq);

@@ -77,7 +77,10 @@ __global__ void __launch_bounds__(kThreads)
     double t = 0.0;
     for (int i = lane; i < nparts; i += 32) t = (OP == RED_MAXABS) ? fmax(t, p[i]) : t + p[i];
     t = (OP == RED_MAXABS) ? warp_max(t) : warp_sum(t);
-    if (lane == 0) out[c] = t;
+    if (lane == 0) {
+      out[c] = t;
+      fence_results();
+    }
   }
   publish_flag(flag, seq);
 }
@@ -144,6 +147,7 @@ namespace {
 __global__ void publish_kernel(const double* __restrict__ src, double* __restrict__ dst, int count,
                                uint64_t* flag, uint64_t seq) {
   for (int i = threadIdx.x; i < count; i += blockDim.x) dst[i] = src[i];
+  fence_results();
   publish_flag(flag, seq);
 }
 }  // namespace
