@@ -1,0 +1,338 @@
+#!/usr/bin/env python
+"""bench.py — Block GMRES block-iterations/s (BASELINE.json metric) on the B200 path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+One "step" = one complete solve of the workload through the unmodified Belos::BlockGmresSolMgr
+driving the B200 plugin classes (X0 = 0 -> relative residual 1e-8): one pass of the hot path over
+one batch of right-hand sides.  N=1 workload = BASELINE configs[1] (Galeri Laplace3D 100^3, block size
+4, 50 blocks, DGKS).  N>1 (launched by torchrun, one rank per GPU): the SAME problem, rows block-
+partitioned over the ranks (strong scaling), halo exchange + small allreduces over NCCL.
+
+JSON line (rank 0): value = block iterations / s with inputs resident in HBM (CUDA events on the
+compute stream, max over ranks); e2e = the same through the C-ABI with HOST buffers (pinned host ->
+device copy of B and X0, solve, device -> host copy of X inside the timed region); roofline = the
+dominant kernel class (MvTransMv Gram) measured with CUDA events around every launch in one extra,
+instrumented step after the timed ones (so the event records do not perturb `value`);
+cpu_baseline = the reference's own Epetra/Belos code (oracle/_ref) on the host cores, bounded sample.
+
+`--impl reference`: the reference's own CPU implementation (oracle/_ref: Epetra + Belos compiled
+from the reference sources; Epetra OpenMP loops + threaded BLAS on all host cores), each step =
+the first restart cycle (Num Blocks block iterations) of the same solve.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+# reference arm: idle OpenMP workers must sleep while the (separately threaded) BLAS runs, and vice versa
+os.environ.setdefault("OMP_WAIT_POLICY", "PASSIVE")
+
+WORKLOADS = {
+    # name: (matrix, dims, block size, num blocks, ortho, tol, BASELINE config index)
+    "laplace2d_100_b1": ("Laplace2D", (100, 100, 1), 1, 50, "DGKS", 1e-8, 0),
+    "laplace3d_100_b4": ("Laplace3D", (100, 100, 100), 4, 50, "DGKS", 1e-8, 1),
+    "laplace3d_200_b4": ("Laplace3D", (200, 200, 200), 4, 50, "DGKS", 1e-8, 2),
+    "brick3d_150_b8": ("Brick3D", (150, 150, 150), 8, 50, "ICGS", 1e-8, 3),
+    "recirc2d_2000_b16": ("Recirc2D", (2000, 2000, 1), 16, 100, "DGKS", 1e-8, 4),
+}
+METRIC = "block_gmres_block_iterations_per_s"
+UNIT = "block-iterations/s"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.lines, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def best_threads(solve_probe):
+    """The reference gets the thread count that serves it best on this host (probe: a few block
+    iterations per candidate); small problems run fastest on one thread, config-2-sized ones on all."""
+    from oracle import ref
+    cores = ref.max_threads()
+    best, best_t = 1, None
+    for th in sorted({1, max(1, cores // 2), cores}):
+        ref.set_threads(th)
+        t0 = time.perf_counter()
+        solve_probe()
+        dt = time.perf_counter() - t0
+        if best_t is None or dt < best_t:
+            best, best_t = th, dt
+    ref.set_threads(best)
+    return best
+
+
+def reference_arm(args, wl):
+    """The reference's own CPU implementation of the path (oracle/_ref), all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import ref
+    name, dims, b, m, ortho, tol, cfg = WORKLOADS[wl]
+    if not ref.available():
+        import oracle  # noqa: F401
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref was not built"}))
+        return 0
+    n, rp, ci, va = _ref_matrix(name, dims)
+    xe, _ = ref.random(1, n, b)
+    B = ref.apply(rp, ci, va, xe)
+    sample_iters = m  # one restart cycle: the basis grows 0 -> b*m, i.e. every kernel shape of the solve
+    cores = best_threads(lambda: ref.block_gmres(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=min(m, 8),
+                                                 max_restarts=1000, tol=tol, ortho=ortho))
+
+    def step():
+        _, r = ref.block_gmres(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=sample_iters, max_restarts=1000,
+                               tol=tol, ortho=ortho)
+        return r["num_iters"], r["solve_seconds"]
+
+    for _ in range(args.warmup):
+        step()
+    iters, secs = 0, 0.0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        it, s = step()
+        iters += it
+        secs += s
+    wall = time.perf_counter() - t0
+    val = iters / secs
+    sample = (f"first restart cycle ({sample_iters} block iterations, basis width 0->{b * m}) of the {wl} solve, "
+              f"Epetra OpenMP loops + OpenBLAS 0.3.15 on {cores} of {ref.max_threads()} host threads (best of 1/half/all)")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * wall / max(args.steps, 1), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wl, "baseline_config": cfg, "matrix": name, "dims": list(dims), "n": n, "block_size": b,
+                   "num_blocks": m, "ortho": ortho, "tol": tol},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+    return 0
+
+
+def _ref_matrix(name, dims):
+    from oracle import ref
+    if name == "Brick3D":  # Galeri-Epetra has no Brick3D: restated stencil fed to Epetra as CSR
+        import oracle
+        return oracle.galeri_csr(name, *dims)
+    return ref.galeri(name, *dims)
+
+
+def cpu_baseline(wl):
+    from oracle import ref
+    name, dims, b, m, ortho, tol, _ = WORKLOADS[wl]
+    if not ref.available():
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    n, rp, ci, va = _ref_matrix(name, dims)
+    xe, _ = ref.random(1, n, b)
+    B = ref.apply(rp, ci, va, xe)
+    cores = best_threads(lambda: ref.block_gmres(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=min(m, 8),
+                                                 max_restarts=1000, tol=tol, ortho=ortho))
+    _, r = ref.block_gmres(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=m, max_restarts=1000, tol=tol, ortho=ortho)
+    ref.set_threads(1)
+    return {"value": r["num_iters"] / r["solve_seconds"], "unit": UNIT, "cores": cores, "kind": "reference",
+            "sample": f"first restart cycle ({r['num_iters']} block iterations, basis width 0->{b * m}) of the same solve; "
+                      f"reference Epetra/Belos (oracle/_ref), Epetra OpenMP + OpenBLAS on {cores} of {ref.max_threads()} host threads (best of 1/half/all), "
+                      f"{r['solve_seconds']:.1f} s"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = args.workload or "laplace3d_100_b4"
+    if args.impl == "reference":
+        return reference_arm(args, wl)
+
+    import numpy as np
+    import torch
+    import trilinos_b200 as tb
+    name, dims, b, m, ortho, tol, cfg = WORKLOADS[wl]
+    warmup = max(args.warmup, 3)
+    ctx, rank, world = tb.dist.init_from_env()
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    local_rank = ctx.device
+    torch.cuda.set_device(local_rank)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
+
+    def barrier():
+        ctx.sync()
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    op, n, lo, hi = tb.dist.local_operator(ctx, name, dims)
+    nloc = hi - lo
+    ctx.set_seed(1)
+    Xe = tb.dist.local_multivec(ctx, n, lo, hi, b, zero=False)
+    Xe.MvRandom()                       # Epetra LCG, seed 1, partition-independent stream
+    B = tb.dist.local_multivec(ctx, n, lo, hi, b)
+    op.Apply(Xe, B)
+    X = tb.dist.local_multivec(ctx, n, lo, hi, b)
+    mgr = tb.BlockGmresSolMgr(op, block_size=b, num_blocks=m, max_iters=-1, max_restarts=100000, tol=tol, ortho=ortho)
+
+    def solve_resident():
+        X.MvInit(0.0)
+        return mgr.solve(X, B)
+
+    # ---- value: inputs resident in HBM --------------------------------------------------------
+    for _ in range(warmup):
+        r = solve_resident()
+    if not r["converged"] or max(r["true_rel_resid"]) > tol * 1.001:
+        raise SystemExit(f"solve did not converge: {r}")
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    l0, s0 = ctx.counters()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    iters = 0
+    e0.record(stream)
+    for _ in range(args.steps):
+        r = solve_resident()
+        iters += r["num_iters"]
+    e1.record(stream)
+    barrier()
+    l1, s1 = ctx.counters()
+    clocks = sampler.stop() if sampler else None
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local_rank}")
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    ms = float(t.item())
+    value = iters / (ms * 1e-3)
+
+    # ---- e2e: host buffers through the C-ABI ---------------------------------------------------
+    Bh = torch.empty((b, nloc), dtype=torch.float64).pin_memory()      # column-major n x b
+    X0h = torch.zeros((b, nloc), dtype=torch.float64).pin_memory()
+    Xh = torch.empty((b, nloc), dtype=torch.float64).pin_memory()
+    Bh.numpy()[:] = B.to_numpy().T
+    import ctypes as C
+    from trilinos_b200._lib import check, lib, c_dbl
+    P = C.POINTER(c_dbl)
+    Bd = tb.dist.local_multivec(ctx, n, lo, hi, b, zero=False)
+    Xd = tb.dist.local_multivec(ctx, n, lo, hi, b, zero=False)
+    ldh = max(nloc, 1)
+
+    def solve_e2e():
+        check(lib.b200_mv_copy_from_host(Bd._h, C.cast(Bh.data_ptr(), P), ldh))
+        check(lib.b200_mv_copy_from_host(Xd._h, C.cast(X0h.data_ptr(), P), ldh))
+        rr = mgr.solve(Xd, Bd)
+        check(lib.b200_mv_copy_to_host(Xd._h, C.cast(Xh.data_ptr(), P), ldh))
+        return rr
+
+    solve_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_iters = 0
+    for _ in range(args.steps):
+        e2e_iters += solve_e2e()["num_iters"]
+    barrier()
+    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local_rank}")
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    e2e_val = e2e_iters / float(t.item())
+    err = float(np.abs(Xh.numpy().T - Xe.to_numpy()).max())
+
+    # ---- roofline: one extra instrumented step (CUDA events around every launch) ---------------
+    ctx.timing_read(reset=True)
+    ctx.timing_enable(True)
+    solve_resident()
+    ctx.timing_enable(False)
+    tm = ctx.timing_read(reset=True)
+    peak, peak_src = peaks()
+    kern = {}
+    for k, v in tm.items():
+        if v["calls"]:
+            gbs = v["bytes"] / (v["ms"] * 1e-3) / 1e9 if v["ms"] > 0 else 0.0
+            kern[k] = {"calls": v["calls"], "ms": round(v["ms"], 3), "algorithmic_GB": round(v["bytes"] / 1e9, 3),
+                       "GBps": round(gbs, 1), "frac": round(gbs / peak, 3)}
+    dom = max(kern, key=lambda k: kern[k]["ms"]) if kern else None
+    roofline = None
+    if dom:
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
+                    "frac": kern[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                    "launches": kern[dom]["calls"], "kernels": kern}
+
+    if rank == 0:
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
+            "ms_per_step": ms / max(args.steps, 1), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": wl, "baseline_config": cfg, "matrix": name, "dims": list(dims), "n": n, "block_size": b,
+                       "num_blocks": m, "ortho": ortho, "tol": tol, "iters_per_solve": r["num_iters"],
+                       "l2": "inputs larger than L2 (Krylov basis %.2f GB per GPU)" % (nloc * 8.0 * b * (m + 1) / 1e9),
+                       "partition": f"1-D row blocks over {world} rank(s)", "max_abs_err_vs_x_exact": err},
+            "clocks": clocks, "gpu_launches": int(l1 - l0), "host_syncs": int(s1 - s0),
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(2 * nloc * b * 8 * world),
+                    "d2h_bytes_per_step": int(nloc * b * 8 * world)},
+            "roofline": roofline,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(wl)
+        print(json.dumps(out))
+    barrier()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

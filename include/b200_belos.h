@@ -167,6 +167,14 @@ int64_t b200_build_colmap(int64_t n_global, int nranks, int rank, int64_t nnz,
                           const int64_t* colind_global, int32_t* colind_local,
                           int64_t* ghost_gids, int32_t* ghost_owner);
 
+/* Halo plan, host part (replaces the Epetra_Import constructor, epetra/src/Epetra_Import.cpp:319-460):
+ * recv side: per-owner counts and offsets into the ghost tail (ghosts are grouped by owner);
+ * send side: global ids the peers asked for -> local row ids to pack (ExportLIDs). */
+int b200_halo_recv_plan(int nranks, int64_t n_ghost, const int32_t* ghost_owner, int64_t* need_cnt,
+                        int64_t* recv_off);
+int b200_halo_send_index(int64_t n_global, int nranks, int rank, int64_t n_asked,
+                         const int64_t* asked_gids, int32_t* send_idx);
+
 /* Galeri-style generators (galeri/src-epetra/Galeri_CrsMatrices.cpp:273-416,
  * CrsMatrices/Galeri_Cross2D.h, Galeri_Cross3D.h, Galeri_Recirc2D.h;
  * Brick3D: galeri/src-xpetra/Galeri_XpetraMatrixTypes.hpp:531-633) on the

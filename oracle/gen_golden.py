@@ -1,0 +1,132 @@
+"""Generates tests/golden/*.npz from the REFERENCE's own compiled code (oracle/_ref, see
+oracle/Makefile.ref).  Run in the build container (needs /root/reference to have built
+oracle/_ref); the fixtures are committed and travel to the GPU box.
+
+    python oracle/gen_golden.py            # kernel + small-solve fixtures (seconds)
+    python oracle/gen_golden.py --full     # additionally BASELINE config 1/2-sized solves (minutes)
+
+Every array below is an output of reference code on explicit, seeded inputs:
+  ref_galeri_*.npz   Galeri::CreateCrsMatrix on the "Linear" map                 (CSR, global ids)
+  ref_kernels.npz    Belos::MultiVecTraits<double,Epetra_MultiVector> ops, Epetra_CrsMatrix::Multiply,
+                     Epetra_MultiVector::Random with explicit seeds
+  ref_solves.json    Belos::BlockGmresSolMgr<double,Epetra_MultiVector,Epetra_Operator>: iteration counts,
+                     achieved tolerance and true residuals for X_exact = LCG(seed 1), B = A X_exact, X0 = 0
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import oracle  # noqa: E402
+from oracle import ref  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+GALERI_CASES = [("Laplace2D", (10, 8, 1), {}), ("Laplace2D", (100, 100, 1), {}), ("Laplace3D", (7, 6, 5), {}),
+                ("Laplace3D", (20, 20, 20), {}), ("Recirc2D", (12, 9, 1), dict(conv=1.0, diff=1e-5)),
+                ("Recirc2D", (40, 40, 1), dict(conv=1.0, diff=1e-5))]
+
+# (label, matrix, dims, block size, num blocks, ortho, tol, max restarts[, max iters; default -1 = n/b - 1])
+SOLVES_SMALL = [
+    ("laplace3d_10_b1_dgks", "Laplace3D", (10, 10, 10), 1, 50, "DGKS", 1e-5, 15),   # the reference's registered example
+    ("laplace3d_10_b1_icgs", "Laplace3D", (10, 10, 10), 1, 50, "ICGS", 1e-5, 15),
+    ("laplace3d_10_b1_imgs", "Laplace3D", (10, 10, 10), 1, 50, "IMGS", 1e-5, 15),
+    ("laplace3d_20_b4_dgks", "Laplace3D", (20, 20, 20), 4, 50, "DGKS", 1e-8, 200),
+    ("laplace3d_20_b4_icgs", "Laplace3D", (20, 20, 20), 4, 25, "ICGS", 1e-8, 200),
+    ("laplace2d_40_b2_dgks", "Laplace2D", (40, 40, 1), 2, 30, "DGKS", 1e-8, 200),
+    ("recirc2d_40_b16_dgks", "Recirc2D", (40, 40, 1), 16, 40, "DGKS", 1e-5, 200, 1000),
+    ("brick3d_12_b8_icgs", "Brick3D", (12, 12, 12), 8, 30, "ICGS", 1e-8, 200),
+]
+SOLVES_FULL = [
+    ("config1_laplace2d_100_b1_dgks", "Laplace2D", (100, 100, 1), 1, 50, "DGKS", 1e-8, 1000),
+    ("config2_laplace3d_100_b4_dgks", "Laplace3D", (100, 100, 100), 4, 50, "DGKS", 1e-8, 1000),
+]
+
+
+def matrix(name, dims, **kw):
+    if name == "Brick3D":  # no Brick3D in Galeri-Epetra: the restated stencil is fed to Epetra as CSR
+        return oracle.galeri_csr(name, *dims)
+    return ref.galeri(name, *dims, **kw)
+
+
+def gen_galeri():
+    for name, dims, kw in GALERI_CASES:
+        n, rp, ci, va = ref.galeri(name, *dims, **kw)
+        fn = os.path.join(OUT, f"ref_galeri_{name}_{dims[0]}x{dims[1]}x{dims[2]}.npz")
+        np.savez_compressed(fn, n=n, rowptr=rp, colind=ci, values=va, dims=np.array(dims),
+                            conv=kw.get("conv", 0.0), diff=kw.get("diff", 0.0))
+        print("wrote", fn, n, len(va))
+
+
+def gen_kernels():
+    rng = np.random.default_rng(20261104)
+    d = {}
+    n, p, q = 1237, 9, 4
+    A = np.asfortranarray(rng.uniform(-1, 1, (n, p)))
+    V = np.asfortranarray(rng.uniform(-1, 1, (n, q)))
+    W = np.asfortranarray(rng.uniform(-1, 1, (n, q)))
+    Bm = np.asfortranarray(rng.uniform(-1, 1, (p, q)))
+    d.update(A=A, V=V, W=W, Bm=Bm)
+    d["trans_mv"] = ref.trans_mv(1.5, A, V)
+    d["times_mat_add_mv_m1_1"] = ref.times_mat_add_mv(-1.0, A, Bm, 1.0, V)
+    d["times_mat_add_mv_1_0"] = ref.times_mat_add_mv(1.0, A, Bm, 0.0, V)
+    d["times_mat_add_mv_h_2"] = ref.times_mat_add_mv(0.5, A, Bm, 2.0, V)
+    d["dot"] = ref.dot(V, W)
+    d["dot_self"] = ref.dot(V, V)
+    for t, nm in ((0, "one"), (1, "two"), (2, "inf")):
+        d["norm_" + nm] = ref.norm(A, t)
+    d["add_mv_gen"] = ref.add_mv(2.5, V, -0.75, W)
+    d["add_mv_m1_1"] = ref.add_mv(-1.0, V, 1.0, W)
+    d["add_mv_1_0"] = ref.add_mv(1.0, V, 0.0, W)
+    d["add_mv_0_1"] = ref.add_mv(0.0, V, 1.0, W)
+    sc = np.array([1.0, 0.0, -2.0, 0.5])
+    d["scale_cols_alpha"] = sc
+    d["scale_cols"] = ref.scale_cols(sc, V)
+    for seed in (1, 12345, 2147483646):
+        y, s = ref.random(seed, 501, 3)
+        d[f"random_{seed}"] = y
+        d[f"random_{seed}_next"] = np.int64(s)
+    for name, dims, kw in (("Laplace3D", (7, 6, 5), {}), ("Recirc2D", (12, 9, 1), dict(conv=1.0, diff=1e-5)),
+                           ("Laplace2D", (10, 8, 1), {})):
+        nn, rp, ci, va = ref.galeri(name, *dims, **kw)
+        X = np.asfortranarray(rng.uniform(-1, 1, (nn, 5)))
+        d[f"apply_{name}_X"] = X
+        d[f"apply_{name}_Y"] = ref.apply(rp, ci, va, X)
+    fn = os.path.join(OUT, "ref_kernels.npz")
+    np.savez_compressed(fn, **d)
+    print("wrote", fn)
+
+
+def gen_solves(cases, fn, threads=1):
+    path = os.path.join(OUT, fn)
+    res = json.load(open(path)) if os.path.exists(path) else {}
+    ref.set_threads(threads)
+    for case in cases:
+        label, name, dims, b, m, ortho, tol, maxr = case[:8]
+        max_iters = case[8] if len(case) > 8 else -1
+        kw = dict(conv=1.0, diff=1e-5) if name == "Recirc2D" else {}
+        n, rp, ci, va = matrix(name, dims, **kw)
+        xe, _ = ref.random(1, n, b)
+        B = ref.apply(rp, ci, va, xe)
+        X, r = ref.block_gmres(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=max_iters, max_restarts=maxr, tol=tol,
+                               ortho=ortho)
+        r.update(matrix=name, dims=list(dims), block_size=b, num_blocks=m, ortho=ortho, tol=tol, max_restarts=maxr, max_iters=max_iters,
+                 rhs="X_exact = Epetra LCG seed 1 (column-major sweep), B = A X_exact, X0 = 0",
+                 max_abs_err=float(np.abs(X - xe).max()), threads=threads)
+        res[label] = r
+        print(label, r["num_iters"], r["converged"], f"{r['solve_seconds']:.2f}s", max(r["true_rel_resid"]), flush=True)
+        json.dump(res, open(path, "w"), indent=1, sort_keys=True)
+    ref.set_threads(1)
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    if "--full" in sys.argv:
+        gen_solves(SOLVES_FULL, "ref_solves_full.json", threads=1)
+    else:
+        gen_galeri()
+        gen_kernels()
+        gen_solves(SOLVES_SMALL, "ref_solves.json")

@@ -79,6 +79,8 @@ _SIGS = {
     "b200_op_info": (C.c_int, [vp, P(c_i64), P(c_i64), P(c_i64), P(c_i64), P(c_i64)]),
     "b200_linear_partition": (C.c_int, [c_i64, C.c_int, C.c_int, P(c_i64), P(c_i64)]),
     "b200_build_colmap": (c_i64, [c_i64, C.c_int, C.c_int, c_i64, P(c_i64), P(c_i32), P(c_i64), P(c_i32)]),
+    "b200_halo_recv_plan": (C.c_int, [C.c_int, c_i64, P(c_i32), P(c_i64), P(c_i64)]),
+    "b200_halo_send_index": (C.c_int, [c_i64, C.c_int, C.c_int, c_i64, P(c_i64), P(c_i32)]),
     "b200_galeri_generate": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_int, c_dbl, c_dbl, c_i64, c_i64,
                                        P(c_i64), P(c_i32), P(c_i64), P(c_dbl)]),
 }

@@ -522,8 +522,11 @@ extern "C" int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_b
     const int P = ctx->nranks, me = ctx->rank;
     // recv side: ghosts are sorted by GID, hence grouped by owner
     std::vector<int64_t> need(P, 0), recv_off(P, 0);
-    for (int64_t g = 0; g < n_ghost; ++g) need[ghost_owner[g]]++;
-    for (int r = 1; r < P; ++r) recv_off[r] = recv_off[r - 1] + need[r - 1];
+    rc = b200_halo_recv_plan(P, n_ghost, ghost_owner.data(), need.data(), recv_off.data());
+    if (rc) {
+      b200_op_destroy(op);
+      return rc;
+    }
     // everyone learns the full P x P "needs" matrix (row = requester)
     std::vector<int64_t> M((size_t)P * P, 0);
     for (int r = 0; r < P; ++r) M[(size_t)me * P + r] = need[r];
@@ -570,13 +573,10 @@ extern "C" int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_b
       return rc;
     }
     std::vector<int32_t> send_idx((size_t)n_send);
-    for (int64_t i = 0; i < n_send; ++i) {
-      const int64_t g = asked[i];
-      if (g < rb || g >= re) {
-        b200_op_destroy(op);
-        return fail(B200_ERR_ARG, "halo setup: a peer asked for a row this rank does not own");
-      }
-      send_idx[i] = (int32_t)(g - rb);
+    rc = b200_halo_send_index(n_global, P, me, n_send, asked.data(), send_idx.data());
+    if (rc) {
+      b200_op_destroy(op);
+      return rc;
     }
     op->n_send = n_send;
     rc = upload(&op->send_idx, send_idx);

@@ -83,6 +83,44 @@ extern "C" int64_t b200_build_colmap(int64_t n_global, int nranks, int rank, int
   return nghost;
 }
 
+// ------------------------------------------------------------------ halo plan (host part)
+// Receive side of the Epetra_Import plan (epetra/src/Epetra_Import.cpp:319-460): ghosts are in
+// column-map order, i.e. grouped by owner, so rank r's block is [recv_off[r], recv_off[r]+need[r]).
+extern "C" int b200_halo_recv_plan(int nranks, int64_t n_ghost, const int32_t* ghost_owner,
+                                   int64_t* need_cnt, int64_t* recv_off) {
+  if (nranks <= 0 || n_ghost < 0 || (n_ghost > 0 && !ghost_owner) || !need_cnt || !recv_off)
+    return b200::fail(B200_ERR_ARG, "b200_halo_recv_plan: bad arguments");
+  for (int r = 0; r < nranks; ++r) need_cnt[r] = 0;
+  int prev = -1;
+  for (int64_t g = 0; g < n_ghost; ++g) {
+    const int o = ghost_owner[g];
+    if (o < 0 || o >= nranks || o < prev)
+      return b200::fail(B200_ERR_ARG, "b200_halo_recv_plan: ghosts are not grouped by ascending owner");
+    prev = o;
+    need_cnt[o]++;
+  }
+  recv_off[0] = 0;
+  for (int r = 1; r < nranks; ++r) recv_off[r] = recv_off[r - 1] + need_cnt[r - 1];
+  return B200_OK;
+}
+
+// Send side: the global ids my peers asked for (concatenated by peer rank) become local row
+// ids to pack (Epetra_Import's ExportLIDs).  Every id must be owned by this rank.
+extern "C" int b200_halo_send_index(int64_t n_global, int nranks, int rank, int64_t n_asked,
+                                    const int64_t* asked_gids, int32_t* send_idx) {
+  int64_t rb, re;
+  if (b200_linear_partition(n_global, nranks, rank, &rb, &re) != 0) return B200_ERR_ARG;
+  if (n_asked < 0 || (n_asked > 0 && (!asked_gids || !send_idx)))
+    return b200::fail(B200_ERR_ARG, "b200_halo_send_index: bad arguments");
+  for (int64_t i = 0; i < n_asked; ++i) {
+    const int64_t g = asked_gids[i];
+    if (g < rb || g >= re)
+      return b200::fail(B200_ERR_ARG, "halo setup: a peer asked for a row this rank does not own");
+    send_idx[i] = (int32_t)(g - rb);
+  }
+  return B200_OK;
+}
+
 // ------------------------------------------------------------------ Galeri
 namespace {
 
