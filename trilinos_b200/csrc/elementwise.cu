@@ -109,7 +109,26 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// bench hygiene: sweep a > L2-sized buffer with loads, leaving L2 full of CLEAN lines (a memset
+// would leave ~126 MB of dirty lines whose write-back steals HBM bandwidth from the timed kernel)
+__global__ void __launch_bounds__(kThreads) l2_sweep_kernel(const double* __restrict__ x,
+                                                            int64_t nvec, double* sink) {
+  double acc = 0.0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const double4v v = ld_plain4(x + 4 * i);
+    acc += v.x + v.y + v.z + v.w;
+  }
+  if (acc == 123.456) *sink = acc;  // never true for a zero-filled buffer; keeps the loads alive
+}
+
 }  // namespace
+
+int launch_l2_sweep(Ctx* ctx, const double* buf, size_t bytes, double* sink) {
+  l2_sweep_kernel<<<kNumSM * 8, kThreads, 0, ctx->stream>>>(buf, (int64_t)(bytes / 32), sink);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
 
 int launch_fill(Ctx* ctx, double* y, int64_t ld, int64_t n, int k, double a) {
   if (n <= 0 || k <= 0) return 0;

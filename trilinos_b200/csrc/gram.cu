@@ -6,15 +6,28 @@
 //   -> Epetra_MultiVector::Multiply('T','N',alpha,A,V,0)   epetra/src/Epetra_MultiVector.cpp:1936-2083
 //   -> local DGEMM + Reduce() (SumAll)                     :2400-2433
 //
-// Design (HBM-bound, algorithmic bytes 8 n (p + q)):
-//   * A is streamed from HBM exactly once with 256-bit evict-first loads; V (n x q, <= a few
-//     tens of MB) is kept L2/L1 resident with evict-last loads and re-read by every column block.
-//   * grid = (row ranges) x (column blocks); inside a CTA the 8 warps are arranged as
-//     WC column groups x WR row groups; a warp owns CPW columns of A and all Q columns of V,
-//     a lane owns 4 consecutive rows per step, so it keeps CPW*Q FP64 accumulators for the
-//     whole row range (no per-tile reduction).
-//   * per-CTA partials go to a workspace laid out [entry][part]; the CTA that arrives last
-//     folds them in a fixed order (deterministic) and publishes to the host mailbox.
+// Design (HBM-bound, algorithmic bytes 8 n (p + q)).  The first version of this kernel kept the
+// streamed operand in registers (8 x 32-byte loads per thread per step) and reached only ~40 % of
+// the HBM roofline: with ~64 KB in flight per SM the kernel is latency-, not bandwidth-bound.
+// This version decouples bytes-in-flight from registers:
+//   * persistent grid, one CTA per SM; CTA i owns a contiguous range of 64*SUB-row tiles and walks
+//     all column blocks (TC = 8*CPW columns of A) of its rows, so every CTA streams the same number
+//     of bytes and V (re-read once per column block) stays L2 resident;
+//   * one elected producer thread moves each (row tile x column block) slab of A plus the matching
+//     V tile into a shared-memory ring with ONE 2-D TMA tensor copy each (cp.async.bulk.tensor.2d,
+//     box = R rows x TC columns; rows >= n and columns >= p are zero-filled by the TMA unit, so
+//     there is no tail masking), completion counted on an mbarrier per stage; up to ~200 KB per SM
+//     are in flight.  (A first TMA version issued one 1-D bulk copy per column: ptxas serialises
+//     those over the lanes with an ELECT/R2UR loop, ~36 copies per 36 KB stage, and the producer
+//     became the bottleneck at 53 % of the HBM roofline.)
+//   * 8 consumer warps read the stage with conflict-free 128-bit LDS (lane = 2 rows), arranged as
+//     WC column groups x WR row groups; a thread keeps CPW*Q FP64 accumulators for the whole row
+//     range of the CTA (no per-tile reduction);
+//   * per-CTA partials go to a workspace laid out [cta][entry]; the CTA that arrives last folds
+//     them in a fixed order (deterministic, run-to-run reproducible) and publishes to the host
+//     mailbox (or to the device buffer the NCCL allreduce works on).
+#include <cuda.h>
+
 #include "device_utils.cuh"
 #include "runtime.cuh"
 
@@ -22,131 +35,292 @@ namespace b200 {
 
 namespace {
 
-constexpr int kThreads = 256;
-constexpr int kWarps = 8;
-constexpr int kRowsPerWarpStep = 128;  // 32 lanes x 4 rows
+constexpr int kMaxStages = 8;
+constexpr size_t kSmemBudget = 200u << 10;
+constexpr int kTC = 32;  // columns of A per column block
 
-template <int Q, int CPW>
-__global__ void __launch_bounds__(kThreads, 2)
-    gram_kernel(const double* __restrict__ A, int64_t lda, int p, const double* __restrict__ V,
-                int64_t ldv, int64_t n, int64_t rows_per_cta, int wc_log2, double alpha,
-                double* __restrict__ ws, int nparts_pad, unsigned int* ticket,
-                double* __restrict__ out, int ldc, uint64_t* flag, uint64_t seq) {
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+// 2-D TMA tensor copy global -> shared (coordinates: c0 = row, c1 = column), completion on an
+// mbarrier (SASS: UTMALDG)
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* tmap, int c0, int c1,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::
+          "r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ double2 lds128(uint32_t addr) {
+  double2 v;
+  asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+  return v;
+}
+template <int NTHREADS>
+__device__ __forceinline__ void consumer_bar() {
+  asm volatile("bar.sync 1, %0;" ::"n"(NTHREADS) : "memory");
+}
+
+struct GramArgs {
+  const double* A;
+  const double* V;
+  int64_t lda, ldv, n;
+  int p, q;          // columns of A, columns of V handled by this launch (q <= Q)
+  int sub;           // 64-row substeps per tile (tile rows R = 64*sub)
+  int nstage;
+  int wc_log2;       // consumer warps = WC column groups x WR row groups
+  int64_t ntiles;    // ceil(n / R)
+  double alpha;
+  double* ws;        // [cta][p*q] partial sums
+  unsigned int* ticket;
+  double* out;       // C(:, 0..q) with leading dimension ldc
+  int ldc;
+  uint64_t* flag;
+  uint64_t seq;
+};
+
+// Q: accumulator columns (>= q), CPW: columns of A per warp, NW: consumer warps.
+// Consumer warp w = (wr, wc): column group wc (CPW columns), row group wr; a warp reads 64 rows
+// (2 per lane, one conflict-free LDS.128 per column) per substep.
+template <int Q, int CPW, int NW>
+__global__ void __launch_bounds__((NW + 1) * 32, 1)
+    gram_tma_kernel(const GramArgs g, const __grid_constant__ CUtensorMap tmA,
+                    const __grid_constant__ CUtensorMap tmV) {
+  constexpr int NT = (NW + 1) * 32;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint64_t full_bar[kMaxStages], empty_bar[kMaxStages];
+  __shared__ double red[NW][CPW * Q];
+
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int WC = 1 << wc_log2, WR = kWarps >> wc_log2;
-  const int wc = warp & (WC - 1), wr = warp >> wc_log2;
-  const int col0 = (blockIdx.y * WC + wc) * CPW;
-  const int64_t r_begin = (int64_t)blockIdx.x * rows_per_cta;
-  const int64_t r_end = min(n, r_begin + rows_per_cta);
+  const int R = 64 * g.sub;
+  const int ncb = (g.p + kTC - 1) / kTC;
+  // stage width: a full column block, rounded up to whole warp column groups (the TMA unit
+  // zero-fills columns >= p, so no lane ever reads shared memory that was not written)
+  const int wfull = min((g.p + CPW - 1) / CPW * CPW, kTC);
+  const uint32_t stage_bytes = (uint32_t)((wfull + g.q) * R) * 8u;
+  unsigned char* stage0 = reinterpret_cast<unsigned char*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  const int64_t t_begin = g.ntiles * blockIdx.x / gridDim.x;
+  const int64_t t_end = g.ntiles * (blockIdx.x + 1) / gridDim.x;
+  const int ntile_cta = (int)(t_end - t_begin);
 
-  double acc[CPW][Q];
-#pragma unroll
-  for (int c = 0; c < CPW; ++c)
-#pragma unroll
-    for (int k = 0; k < Q; ++k) acc[c][k] = 0.0;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < g.nstage; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], NW);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
 
-  const double* Ap[CPW];
-#pragma unroll
-  for (int c = 0; c < CPW; ++c) Ap[c] = A + (size_t)min(col0 + c, p - 1) * lda;
-
-  if (col0 < p) {
-    for (int64_t r = r_begin + (int64_t)wr * kRowsPerWarpStep + lane * 4; r < r_end;
-         r += (int64_t)kRowsPerWarpStep * WR) {
-      double4v a[CPW], v[Q];
-#pragma unroll
-      for (int c = 0; c < CPW; ++c) a[c] = ld_stream4(Ap[c] + r);
-#pragma unroll
-      for (int k = 0; k < Q; ++k) v[k] = ld_keep4(V + (size_t)k * ldv + r);
-      if (r + 3 >= n) {  // last, partial 4-row vector: padding rows must not contribute
-#pragma unroll
-        for (int c = 0; c < CPW; ++c) {
-          if (r + 1 >= n) a[c].y = 0.0;
-          if (r + 2 >= n) a[c].z = 0.0;
-          if (r + 3 >= n) a[c].w = 0.0;
-        }
-#pragma unroll
-        for (int k = 0; k < Q; ++k) {
-          if (r + 1 >= n) v[k].y = 0.0;
-          if (r + 2 >= n) v[k].z = 0.0;
-          if (r + 3 >= n) v[k].w = 0.0;
+  if (warp == NW) {
+    // ------------------------------------------------------------------ producer (one thread)
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int cb = 0; cb < ncb; ++cb) {
+        const int col0 = cb * kTC;
+        for (int t = 0; t < ntile_cta; ++t) {
+          mbar_wait(&empty_bar[s], ph ^ 1u);
+          const int r0 = (int)((t_begin + t) * R);
+          unsigned char* st = stage0 + (size_t)s * stage_bytes;
+          mbar_expect_tx(&full_bar[s], stage_bytes);
+          tma_load_2d(st, &tmA, r0, col0, &full_bar[s]);
+          tma_load_2d(st + (size_t)wfull * R * 8, &tmV, r0, 0, &full_bar[s]);
+          if (++s == g.nstage) { s = 0; ph ^= 1u; }
         }
       }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------------ consumer warps
+    const int WC = 1 << g.wc_log2, WR = NW >> g.wc_log2;
+    const int wc = warp & (WC - 1), wr = warp >> g.wc_log2;
+    const uint32_t colstride = (uint32_t)R * 8u;
+    const uint32_t base = smem_u32(stage0);
+    const uint32_t a_off = (uint32_t)(wc * CPW) * colstride + (uint32_t)lane * 16u;
+    const uint32_t v_off = (uint32_t)wfull * colstride + (uint32_t)lane * 16u;
+    int s = 0;
+    uint32_t ph = 0;
+    for (int cb = 0; cb < ncb; ++cb) {
+      const int col0 = cb * kTC;
+      const int wdt = min(kTC, g.p - col0);
+      // columns >= p of the last block are zero-filled by the TMA unit: no per-column predicate
+      const bool active = wc * CPW < wdt;
+      double acc[CPW][Q];
+#pragma unroll
+      for (int c = 0; c < CPW; ++c)
+#pragma unroll
+        for (int k = 0; k < Q; ++k) acc[c][k] = 0.0;
+
+      for (int t = 0; t < ntile_cta; ++t) {
+        mbar_wait(&full_bar[s], ph);
+        if (active) {
+          const uint32_t st = base + (uint32_t)s * stage_bytes;
+          for (int ss = wr; ss < g.sub; ss += WR) {
+            const uint32_t row = (uint32_t)ss * 512u;  // 64 rows x 8 bytes
+            double2 a[CPW];
+#pragma unroll
+            for (int c = 0; c < CPW; ++c) a[c] = lds128(st + a_off + row + (uint32_t)c * colstride);
+#pragma unroll
+            for (int k = 0; k < Q; ++k) {
+              if (k < g.q) {
+                const double2 v = lds128(st + v_off + row + (uint32_t)k * colstride);
+#pragma unroll
+                for (int c = 0; c < CPW; ++c) {
+                  acc[c][k] = fma(a[c].x, v.x, acc[c][k]);
+                  acc[c][k] = fma(a[c].y, v.y, acc[c][k]);
+                }
+              }
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[s]);
+        if (++s == g.nstage) { s = 0; ph ^= 1u; }
+      }
+
+      // lanes -> warp, then the WR row-group warps of each column group, then the workspace
 #pragma unroll
       for (int c = 0; c < CPW; ++c)
 #pragma unroll
         for (int k = 0; k < Q; ++k) {
-          acc[c][k] = fma(a[c].x, v[k].x, acc[c][k]);
-          acc[c][k] = fma(a[c].y, v[k].y, acc[c][k]);
-          acc[c][k] = fma(a[c].z, v[k].z, acc[c][k]);
-          acc[c][k] = fma(a[c].w, v[k].w, acc[c][k]);
+          const double sres = warp_sum(acc[c][k]);
+          if (lane == 0) red[warp][c * Q + k] = sres;
         }
+      consumer_bar<NW * 32>();
+      for (int e = threadIdx.x; e < WC * CPW * Q; e += NW * 32) {
+        const int grp = e / (CPW * Q), ck = e % (CPW * Q);
+        const int c = ck / Q, k = ck % Q;
+        const int col = col0 + grp * CPW + c;
+        if (grp * CPW + c < wdt && k < g.q) {
+          double sres = 0.0;
+          for (int w = 0; w < WR; ++w) sres += red[(w << g.wc_log2) + grp][ck];
+          g.ws[(size_t)blockIdx.x * (size_t)(g.p * g.q) + (size_t)k * g.p + col] = sres;
+        }
+      }
+      consumer_bar<NW * 32>();
     }
   }
 
-  // CTA reduction: lanes -> warp, then the WR row-group warps of each column group
-  __shared__ double sm[kWarps][CPW * Q];
-#pragma unroll
-  for (int c = 0; c < CPW; ++c)
-#pragma unroll
-    for (int k = 0; k < Q; ++k) {
-      const double s = warp_sum(acc[c][k]);
-      if (lane == 0) sm[warp][c * Q + k] = s;
-    }
-  __syncthreads();
+  if (!last_cta_arrives(g.ticket, gridDim.x)) return;
+  // deterministic fold over the per-CTA partials: thread = entry, fixed order over CTAs
+  const int nent = g.p * g.q;
   const int nparts = gridDim.x;
-  for (int e = threadIdx.x; e < WC * CPW * Q; e += kThreads) {
-    const int g = e / (CPW * Q), ck = e % (CPW * Q);
-    const int c = ck / Q, k = ck % Q;
-    const int col = (blockIdx.y * WC + g) * CPW + c;
-    if (col < p) {
-      double s = 0.0;
-      for (int w = 0; w < WR; ++w) s += sm[(w << wc_log2) + g][ck];
-      ws[((size_t)k * p + col) * nparts_pad + blockIdx.x] = s;
-    }
-  }
-
-  if (!last_cta_arrives(ticket, gridDim.x * gridDim.y)) return;
-  // deterministic fold over the row-range partials: one warp per output entry
-  const int nent = p * Q;
-  for (int e = warp; e < nent; e += kWarps) {
-    const volatile double* src = ws + (size_t)e * nparts_pad;
+  for (int e = threadIdx.x; e < nent; e += NT) {
+    const double* src = g.ws + e;
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    int i = lane;
-    for (; i + 96 < nparts; i += 128) {
-      s0 += src[i]; s1 += src[i + 32]; s2 += src[i + 64]; s3 += src[i + 96];
+    int i = 0;
+    for (; i + 3 < nparts; i += 4) {
+      s0 += __ldcg(src + (size_t)(i + 0) * nent);
+      s1 += __ldcg(src + (size_t)(i + 1) * nent);
+      s2 += __ldcg(src + (size_t)(i + 2) * nent);
+      s3 += __ldcg(src + (size_t)(i + 3) * nent);
     }
-    for (; i < nparts; i += 32) s0 += src[i];
-    const double s = warp_sum((s0 + s1) + (s2 + s3));
-    if (lane == 0) {
-      const int k = e / p, col = e % p;
-      out[(size_t)k * ldc + col] = alpha * s;
-      fence_results();
-    }
+    for (; i < nparts; ++i) s0 += __ldcg(src + (size_t)i * nent);
+    const int k = e / g.p, col = e % g.p;
+    g.out[(size_t)k * g.ldc + col] = g.alpha * ((s0 + s1) + (s2 + s3));
   }
-  publish_flag(flag, seq);
+  if (g.flag != nullptr) fence_results();
+  publish_flag(g.flag, g.seq);
 }
 
-template <int Q, int CPW>
-int launch_gram_t(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, int64_t ldv,
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// n x ncols FP64 column-major matrix (leading dimension ld) as a 2-D tensor {row, column};
+// box = rows x cols; out-of-bounds elements read as zero
+int make_tmap(CUtensorMap* tm, const double* base, int64_t n, int ncols, int64_t ld, int box_rows,
+              int box_cols) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  const cuuint64_t dims[2] = {(cuuint64_t)n, (cuuint64_t)ncols};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(double)};
+  const cuuint32_t box[2] = {(cuuint32_t)box_rows, (cuuint32_t)box_cols};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(base), dims,
+                         strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return failf(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+template <int Q, int CPW, int NW>
+int launch_gram_t(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, int64_t ldv, int q,
                   int64_t n, double alpha, double* out, int ldc, uint64_t* flag) {
-  // warp arrangement: as many column groups as the block needs (power of two <= 8)
+  static_assert(kTC % CPW == 0 && NW >= kTC / CPW, "one column block must fit the consumer warps");
+  GramArgs g;
+  g.A = A; g.V = V; g.lda = lda; g.ldv = ldv; g.n = n; g.p = p; g.q = q;
+  // warp arrangement: as many column groups as one column block needs (power of two)
+  const int wfull = std::min((p + CPW - 1) / CPW * CPW, kTC);
   int wc_log2 = 0;
-  while ((1 << wc_log2) < kWarps && (1 << wc_log2) * CPW < p) ++wc_log2;
-  const int WC = 1 << wc_log2, WR = kWarps >> wc_log2;
-  const int tc = WC * CPW;
-  const int ncb = (p + tc - 1) / tc;
-  const int64_t step = (int64_t)kRowsPerWarpStep * WR;
-  int target = std::max(1, (2 * kNumSM) / ncb);
-  int64_t rows_per_cta = (n + target - 1) / target;
-  rows_per_cta = std::max<int64_t>(step, (rows_per_cta + step - 1) / step * step);
-  int nparts = (int)std::max<int64_t>(1, (n + rows_per_cta - 1) / rows_per_cta);
-  const int nparts_pad = (nparts + 31) & ~31;
-  if ((size_t)p * Q * nparts_pad * sizeof(double) > kWorkspaceBytes)
+  while ((1 << wc_log2) * CPW < wfull) ++wc_log2;
+  const int WR = NW >> wc_log2;
+  g.wc_log2 = wc_log2;
+  g.sub = std::min(4, std::max(2, WR));  // TMA box rows <= 256
+  const int R = 64 * g.sub;
+  const size_t stage_bytes = (size_t)(wfull + q) * R * sizeof(double);
+  g.nstage = (int)std::max<size_t>(2, std::min<size_t>(kMaxStages, kSmemBudget / stage_bytes));
+  g.ntiles = (n + R - 1) / R;
+  g.alpha = alpha;
+  g.ws = ctx->ws; g.ticket = ctx->ticket; g.out = out; g.ldc = ldc; g.flag = flag; g.seq = ctx->seq;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->num_sms, g.ntiles));
+  if ((size_t)p * q * grid * sizeof(double) > kWorkspaceBytes)
     return fail(B200_ERR_ARG, "MvTransMv: partial-sum workspace too small");
-  dim3 grid((unsigned)nparts, (unsigned)ncb, 1);
-  gram_kernel<Q, CPW><<<grid, kThreads, 0, ctx->stream>>>(A, lda, p, V, ldv, n, rows_per_cta,
-                                                           wc_log2, alpha, ctx->ws, nparts_pad,
-                                                           ctx->ticket, out, ldc, flag, ctx->seq);
+  CUtensorMap tmA, tmV;
+  B200_TRY(make_tmap(&tmA, A, n, p, lda, R, wfull));
+  B200_TRY(make_tmap(&tmV, V, n, q, ldv, R, q));
+  const size_t smem = stage_bytes * g.nstage + 128;
+  static bool attr_set = false;  // per template instantiation
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(gram_tma_kernel<Q, CPW, NW>,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(216u << 10)));
+    attr_set = true;
+  }
+  gram_tma_kernel<Q, CPW, NW><<<grid, (NW + 1) * 32, smem, ctx->stream>>>(g, tmA, tmV);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
   return 0;
@@ -159,22 +333,25 @@ int launch_gram(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, 
   if (p <= 0 || q <= 0) return 0;
   double* out = ctx->result_ptr() + out_off;
   ctx->t_begin(K_GRAM, 8.0 * n * ((double)p + q));
-  // split q greedily into register-resident chunks of 8 / 4 / 2 / 1 columns of V
+  // q is processed in one pass whenever q <= 16 (Q = next supported width; unused accumulator
+  // columns are masked), so A is streamed from HBM exactly once per call
   int k0 = 0;
   int rc = 0;
   while (k0 < q && rc == 0) {
-    const int rem = q - k0;
+    const int step = std::min(16, q - k0);
     const double* Vk = V + (size_t)k0 * ldv;
     double* outk = out + (size_t)k0 * ldc;
-    int step;
-    if (rem >= 8) step = 8; else if (rem >= 4) step = 4; else if (rem >= 2) step = 2; else step = 1;
     uint64_t* flag = (last && k0 + step >= q) ? ctx->result_flag() : nullptr;
-    switch (step) {
-      case 8: rc = launch_gram_t<8, 2>(ctx, A, lda, p, Vk, ldv, n, alpha, outk, ldc, flag); break;
-      case 4: rc = launch_gram_t<4, 4>(ctx, A, lda, p, Vk, ldv, n, alpha, outk, ldc, flag); break;
-      case 2: rc = launch_gram_t<2, 4>(ctx, A, lda, p, Vk, ldv, n, alpha, outk, ldc, flag); break;
-      default: rc = launch_gram_t<1, 4>(ctx, A, lda, p, Vk, ldv, n, alpha, outk, ldc, flag); break;
-    }
+    if (step > 8)
+      rc = launch_gram_t<16, 4, 8>(ctx, A, lda, p, Vk, ldv, step, n, alpha, outk, ldc, flag);
+    else if (step > 4)
+      rc = launch_gram_t<8, 4, 8>(ctx, A, lda, p, Vk, ldv, step, n, alpha, outk, ldc, flag);
+    else if (step > 2)
+      rc = launch_gram_t<4, 4, 16>(ctx, A, lda, p, Vk, ldv, step, n, alpha, outk, ldc, flag);
+    else if (step > 1)
+      rc = launch_gram_t<2, 4, 16>(ctx, A, lda, p, Vk, ldv, step, n, alpha, outk, ldc, flag);
+    else
+      rc = launch_gram_t<1, 4, 16>(ctx, A, lda, p, Vk, ldv, step, n, alpha, outk, ldc, flag);
     k0 += step;
   }
   ctx->t_end();

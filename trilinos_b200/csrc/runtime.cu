@@ -244,6 +244,7 @@ extern "C" int b200_ctx_create(int device, b200_ctx** out) {
   B200_CUDA(cudaSetDevice(device));
   auto* c = new b200_ctx();
   c->device = device;
+  B200_CUDA(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, device));
   B200_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   B200_CUDA(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
   B200_CUDA(cudaEventCreateWithFlags(&c->ev_comm, cudaEventDisableTiming));
@@ -382,7 +383,10 @@ extern "C" void* b200_ctx_stream(b200_ctx* c) { return c ? (void*)c->stream : nu
 extern "C" int b200_ctx_flush_l2(b200_ctx* c) {
   if (!c) return fail(B200_ERR_ARG, "null context");
   const size_t bytes = 256u << 20;  // 2 x the 126 MB L2
-  if (!c->flush_buf) B200_CUDA(cudaMalloc(&c->flush_buf, bytes));
-  B200_CUDA(cudaMemsetAsync(c->flush_buf, 0, bytes, c->stream));
+  if (!c->flush_buf) {
+    B200_CUDA(cudaMalloc(&c->flush_buf, bytes));
+    B200_CUDA(cudaMemsetAsync(c->flush_buf, 0, bytes, c->stream));
+  }
+  B200_TRY(launch_l2_sweep(c, (const double*)c->flush_buf, bytes, c->ws));
   return 0;
 }

@@ -42,6 +42,7 @@ enum KClass { K_SPMM = 0, K_GRAM = 1, K_UPDATE = 2, K_REDUCE = 3, K_AXPBY = 4, K
 
 struct Ctx {
   int device = 0;
+  int num_sms = kNumSM;               // queried at context creation
   cudaStream_t stream = nullptr;       // compute stream (all kernels)
   cudaStream_t comm_stream = nullptr;  // halo exchange
   cudaEvent_t ev_comm = nullptr, ev_compute = nullptr;
@@ -165,6 +166,7 @@ int launch_axpby(Ctx*, double* y, int64_t ldy, const double* a, int64_t lda, con
 int launch_scale_cols(Ctx*, double* y, int64_t ld, int64_t n, int k, const double* alpha_host);
 int launch_random(Ctx*, double* y, int64_t ld, int64_t n, int k, int64_t row_offset,
                   int64_t n_global, int64_t seq_start, unsigned int seed);
+int launch_l2_sweep(Ctx*, const double* buf, size_t bytes, double* sink);
 // reduce.cu : out[j] for j<k written to ctx->result_ptr()+out_off
 int launch_dot(Ctx*, const double* a, int64_t lda, const double* b, int64_t ldb, int64_t n, int k,
                int out_off, bool last);
