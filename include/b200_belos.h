@@ -65,6 +65,14 @@ int b200_ctx_rank(const b200_ctx* ctx, int* rank, int* nranks);
 int b200_ctx_set_seed(b200_ctx* ctx, unsigned int seed);
 /* counters: kernels launched / host syncs since creation (bench "gpu_launches") */
 int b200_ctx_counters(const b200_ctx* ctx, int64_t* launches, int64_t* syncs);
+/* Fused reductions: kernels that write a column (operator apply, MvTimesMatAddMv) also emit
+ * the column inner products Belos' orthogonalisation asks for next, and MvDot / MvNorm(TwoNorm) on columns
+ * whose contents have not changed since their product was computed return it without a launch.  Contents
+ * are tracked by per-column ids; b200_mv_device_ptr() switches tracking off for that storage.
+ * on = 0 disables both (every MvDot / MvNorm launches its own reduction); also B200_NO_FUSE=1 in the
+ * environment.  dot_hits (may be NULL) returns how many column products were served that way. */
+int b200_ctx_set_fusion(b200_ctx* ctx, int on);
+int b200_ctx_fusion_stats(const b200_ctx* ctx, int64_t* dot_hits);
 /* per-kernel-class device timing (CUDA events on the compute stream).
  * classes: 0 spmm, 1 trans_mv, 2 times_mat_add_mv, 3 dot/norm, 4 axpby/scale/copy, 5 halo */
 #define B200_NUM_KCLASS 6

@@ -270,3 +270,81 @@ def test_full_size_properties(ctx):
     d.MvAddMv(1.0, y0, -1.0, q3)
     assert d.MvNorm()[0] <= 1e-12 * q3.MvNorm()[0]
     assert np.all(Y.CloneView([1, 2, 3]).MvNorm() == 0.0)
+
+
+# ----------------------------------------------------------------------------------------------
+# Fused reductions / remembered column products: same values as the standalone
+# reduction kernels (<= 1e-13 vs the oracle), and never a stale value after a column was rewritten.
+@pytest.mark.parametrize("n", [1, 3, 33, 515, 4097, 100003])
+@pytest.mark.parametrize("p,q", [(1, 1), (3, 1), (7, 4), (40, 8), (5, 3)])
+def test_fused_update_dots(ctx, n, p, q):
+    a, v, bm = rnd(n, p, 11), rnd(n, q, 12), rnd(p, q, 13) * 0.1
+    A, V = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, v)
+    Vold = V.CloneCopy()
+    h0 = ctx.dot_hits()
+    V.MvTimesMatAddMv(-1.0, A, bm, 1.0)
+    vnew = oracle.times_mat_add_mv(-1.0, a, bm, 1.0, v)
+    d_self, d_old, nrm = V.MvDot(V), V.MvDot(Vold), V.MvNorm(tb.NORM_TWO)
+    assert ctx.dot_hits() - h0 == 3 * q, "the three reductions after the update must come from its epilogue"
+    assert relerr(V.to_numpy(), vnew) <= TOL
+    assert relerr(d_self, oracle.dot(vnew, vnew)) <= TOL
+    assert np.abs(d_old - oracle.dot(vnew, v)).max() <= TOL * np.sqrt(oracle.dot(vnew, vnew) * oracle.dot(v, v)).max()
+    assert relerr(nrm, oracle.norm(vnew, 1)) <= TOL
+    # same numbers with the fusion switched off (standalone kernels)
+    ctx.set_fusion(False)
+    try:
+        assert relerr(V.MvDot(V), d_self) <= TOL and relerr(V.MvNorm(tb.NORM_TWO), nrm) <= TOL
+        assert np.abs(V.MvDot(Vold) - d_old).max() <= TOL * np.sqrt(oracle.dot(vnew, vnew) * oracle.dot(v, v)).max()
+    finally:
+        ctx.set_fusion(True)
+
+
+def test_remembered_dots_are_invalidated_by_every_write(ctx):
+    n, k = 5003, 3
+    a, b = rnd(n, k, 21), rnd(n, k, 22)
+    A, B = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, b)
+
+    def check():
+        got, ref = A.MvDot(A), oracle.dot(A.to_numpy(), A.to_numpy())
+        assert relerr(got, ref) <= TOL
+        assert relerr(A.MvNorm(tb.NORM_TWO), np.sqrt(ref)) <= TOL
+
+    check()
+    h0 = ctx.dot_hits()
+    check()
+    assert ctx.dot_hits() - h0 == 2 * k            # unchanged columns: served from the memo
+    for write in (lambda: A.MvScale(1.5), lambda: A.MvScale([2.0, 0.5, -1.0]), lambda: A.MvAddMv(1.0, A, 0.25, B),
+                  lambda: A.MvInit(0.75), lambda: A.MvRandom(), lambda: A.set_numpy(b * 3.0),
+                  lambda: A.SetBlock(B, [2, 0, 1]), lambda: A.MvAddMv(0.0, A, 1.0, B),
+                  lambda: A.CloneViewNonConst([1]).MvScale(-3.0),
+                  lambda: A.MvTimesMatAddMv(0.5, B, rnd(k, k, 23), 0.0)):
+        write()
+        h0 = ctx.dot_hits()
+        check()
+    # a copy carries its source's content id: x.x of the copy is known without a launch
+    C2 = A.CloneCopy()
+    h0 = ctx.dot_hits()
+    assert relerr(C2.MvDot(C2), oracle.dot(A.to_numpy(), A.to_numpy())) <= TOL
+    assert ctx.dot_hits() - h0 == k
+    # writing the copy must not poison the original (and vice versa)
+    C2.MvScale(2.0)
+    assert relerr(C2.MvDot(C2), 4.0 * oracle.dot(A.to_numpy(), A.to_numpy())) <= TOL
+    check()
+
+
+@pytest.mark.parametrize("name,dims,k", [("Laplace3D", (9, 8, 7), 4), ("Laplace2D", (33, 31, 1), 1), ("Brick3D", (7, 6, 5), 8),
+                                         ("Recirc2D", (20, 17, 1), 3)])
+def test_fused_apply_dots(ctx, name, dims, k):
+    n, rp, ci, va = tb.galeri(name, *dims)
+    op = tb.CrsOperator(ctx, n, 0, n, rp, ci, va)
+    x = rnd(n, k, 31)
+    X, Y = tb.MultiVec.from_numpy(ctx, x), tb.MultiVec(ctx, n, k)
+    h0 = ctx.dot_hits()
+    op.Apply(X, Y)
+    yref = oracle.spmm(rp, ci.astype(np.int32), va, x)
+    d = Y.MvDot(Y)
+    assert ctx.dot_hits() - h0 == k
+    assert relerr(Y.to_numpy(), yref) <= TOL
+    assert relerr(d, oracle.dot(yref, yref)) <= TOL
+    op.Apply(X, Y)                                  # rewritten: ids change, values identical
+    assert relerr(Y.MvNorm(tb.NORM_TWO), oracle.norm(yref, 1)) <= TOL

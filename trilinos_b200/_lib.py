@@ -47,6 +47,8 @@ _SIGS = {
     "b200_ctx_rank": (C.c_int, [vp, P(C.c_int), P(C.c_int)]),
     "b200_ctx_set_seed": (C.c_int, [vp, C.c_uint]),
     "b200_ctx_counters": (C.c_int, [vp, P(c_i64), P(c_i64)]),
+    "b200_ctx_set_fusion": (C.c_int, [vp, C.c_int]),
+    "b200_ctx_fusion_stats": (C.c_int, [vp, P(c_i64)]),
     "b200_ctx_timing_enable": (C.c_int, [vp, C.c_int]),
     "b200_ctx_timing_read": (C.c_int, [vp, P(c_dbl), P(c_i64), P(c_dbl), C.c_int]),
     "b200_ctx_stream": (vp, [vp]),

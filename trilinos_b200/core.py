@@ -71,6 +71,14 @@ class Context:
         check(lib.b200_ctx_counters(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def set_fusion(self, on=True):
+        check(lib.b200_ctx_set_fusion(self._h, 1 if on else 0))
+
+    def dot_hits(self):
+        a = c_i64()
+        check(lib.b200_ctx_fusion_stats(self._h, C.byref(a)))
+        return a.value
+
     def timing_enable(self, on=True):
         check(lib.b200_ctx_timing_enable(self._h, 1 if on else 0))
 

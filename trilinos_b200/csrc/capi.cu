@@ -43,7 +43,7 @@ int new_mv(Ctx* ctx, int64_t n_local, int64_t n_global, int64_t row_offset, int 
     delete m;
     return rc;
   }
-  m->st = std::make_shared<Storage>(ctx, (double*)p, bytes);
+  m->st = std::make_shared<Storage>(ctx, (double*)p, bytes, ncols);
   m->cols.resize(ncols);
   std::iota(m->cols.begin(), m->cols.end(), 0);
   *out = m;
@@ -60,6 +60,26 @@ bool columns_overlap(const MV* a, const MV* b) {
     for (int cb : b->cols)
       if (ca == cb) return true;
   return false;
+}
+
+// A mailbox slot + sequence number for a kernel with a fused reduction epilogue (single rank
+// only: multi-rank results would still need their allreduce).  Remembered products that were
+// still waiting in the recycled slot are dropped.
+bool fused_slot(Ctx* ctx, FusedDots* fd, size_t* src) {
+  if (!ctx->fuse || ctx->nranks != 1) return false;
+  const int slot = ctx->aux_next;
+  ctx->aux_next = (slot + 1) % kAuxSlots;
+  const size_t base = kAuxBase + (size_t)slot * kAuxSlotDoubles;
+  for (int i = 0; i < kDotCache; ++i)
+    if (ctx->dots[i].seq != 0 && ctx->dots[i].src >= base && ctx->dots[i].src < base + kAuxSlotDoubles)
+      ctx->dots[i] = Ctx::DotEntry();
+  fd->out = ctx->mbox_d + base;
+  fd->flag = ctx->flag_d;
+  fd->seq = ++ctx->seq;
+  fd->ws = ctx->ws;
+  fd->ticket = ctx->ticket;
+  *src = base;
+  return true;
 }
 
 // Park-Miller jump: seed * 16807^e mod (2^31-1)
@@ -149,6 +169,7 @@ extern "C" int b200_mv_clone_copy(const b200_mv* mv, const int* index, int ninde
     }
     j += len;
   }
+  for (int i = 0; i < nindex; ++i) c->copy_id(i, mv, index[i]);  // a copy has its source's content
   *out = c;
   return 0;
 }
@@ -165,6 +186,7 @@ extern "C" int b200_mv_init(b200_mv* mv, double alpha) {
   for (int j = 0; j < mv->ncols();) {
     const int len = run_length(j, mv->ncols(), mv, j);
     B200_TRY(launch_fill(mv->ctx, mv->col(j), mv->ld, mv->n_local, len, alpha));
+    mv->touch(j, len);
     j += len;
   }
   return 0;
@@ -177,6 +199,7 @@ extern "C" int b200_mv_random(b200_mv* mv) {
     const int len = run_length(j, mv->ncols(), mv, j);
     B200_TRY(launch_random(ctx, mv->col(j), mv->ld, mv->n_local, len, mv->row_offset,
                            mv->n_global, (int64_t)j * mv->n_global, ctx->seed));
+    mv->touch(j, len);
     j += len;
   }
   ctx->seed = pm_advance(ctx->seed, (unsigned long long)mv->n_global * mv->ncols());
@@ -200,17 +223,23 @@ extern "C" int b200_mv_add_mv(b200_mv* mv, double alpha, const b200_mv* A, doubl
     const int len = run_length(j, k, mv, j, A, j, B, j);
     if (alpha == 0.0 && beta == 0.0) {
       B200_TRY(launch_fill(ctx, mv->col(j), mv->ld, n, len, 0.0));
+      mv->touch(j, len);
     } else if (alpha == 0.0) {
-      if (!(beta == 1.0 && B->col(j) == mv->col(j)))
+      if (!(beta == 1.0 && B->col(j) == mv->col(j))) {
         B200_TRY(launch_axpby(ctx, mv->col(j), mv->ld, B->col(j), B->ld, nullptr, 0, n, len, beta,
                               0.0));
+        if (beta == 1.0) mv->copy_id(j, B, j, len); else mv->touch(j, len);
+      }
     } else if (beta == 0.0) {
-      if (!(alpha == 1.0 && A->col(j) == mv->col(j)))
+      if (!(alpha == 1.0 && A->col(j) == mv->col(j))) {
         B200_TRY(launch_axpby(ctx, mv->col(j), mv->ld, A->col(j), A->ld, nullptr, 0, n, len,
                               alpha, 0.0));
+        if (alpha == 1.0) mv->copy_id(j, A, j, len); else mv->touch(j, len);
+      }
     } else {
       B200_TRY(launch_axpby(ctx, mv->col(j), mv->ld, A->col(j), A->ld, B->col(j), B->ld, n, len,
                             alpha, beta));
+      mv->touch(j, len);
     }
     j += len;
   }
@@ -224,6 +253,7 @@ extern "C" int b200_mv_scale(b200_mv* mv, double alpha) {
     const int len = run_length(j, mv->ncols(), mv, j);
     B200_TRY(launch_axpby(mv->ctx, mv->col(j), mv->ld, mv->col(j), mv->ld, nullptr, 0,
                           mv->n_local, len, alpha, 0.0));
+    mv->touch(j, len);
     j += len;
   }
   return 0;
@@ -238,6 +268,7 @@ extern "C" int b200_mv_scale_cols(b200_mv* mv, const double* alpha, int nalpha) 
   for (int j = 0; j < mv->ncols();) {
     const int len = run_length(j, mv->ncols(), mv, j);
     B200_TRY(launch_scale_cols(mv->ctx, mv->col(j), mv->ld, mv->n_local, len, alpha + j));
+    mv->touch(j, len);
     j += len;
   }
   return 0;
@@ -259,6 +290,7 @@ extern "C" int b200_mv_set_block(b200_mv* mv, const b200_mv* A, const int* index
                             mv->n_local, len, 1.0, 0.0));
     j += len;
   }
+  for (int i = 0; i < nindex; ++i) mv->copy_id(index[i], A, i);
   return 0;
 }
 
@@ -270,6 +302,22 @@ extern "C" int b200_mv_dot(const b200_mv* mv, const b200_mv* A, double* b, int n
   if (nb < k) return 0;  // reference silently does nothing (BelosEpetraAdapter.cpp:505)
   if (k == 0) return 0;
   Ctx* ctx = mv->ctx;
+  // products a fused epilogue (or an earlier call on unchanged columns) already produced
+  std::vector<uint64_t> ia(k), ib(k);
+  bool known = ctx->fuse;
+  for (int j = 0; j < k; ++j) {
+    ia[j] = mv->id(j);
+    ib[j] = A->id(j);
+  }
+  for (int j = 0; j < k && known; ++j) {
+    int rc = 0;
+    known = ctx->recall_dot(ia[j], ib[j], &b[j], &rc);
+    if (rc) return rc;
+  }
+  if (known) {
+    ctx->dot_hits += k;
+    return 0;
+  }
   ++ctx->seq;
   for (int j = 0; j < k;) {
     const int len = run_length(j, k, mv, j, A, j);
@@ -278,7 +326,10 @@ extern "C" int b200_mv_dot(const b200_mv* mv, const b200_mv* A, double* b, int n
     j += len;
   }
   B200_TRY(ctx->finish_reduction(k, false));
-  for (int j = 0; j < k; ++j) b[j] = ctx->mbox_h[j];
+  for (int j = 0; j < k; ++j) {
+    b[j] = ctx->mbox_h[j];
+    ctx->remember_dot(ia[j], ib[j], b[j]);
+  }
   return 0;
 }
 
@@ -290,6 +341,22 @@ extern "C" int b200_mv_norm(const b200_mv* mv, int type, double* normvec, int nn
   if (nnorm < k) return 0;  // reference silently does nothing (BelosEpetraAdapter.cpp:516)
   if (k == 0) return 0;
   Ctx* ctx = mv->ctx;
+  std::vector<uint64_t> ia(k);
+  for (int j = 0; j < k; ++j) ia[j] = mv->id(j);
+  if (type == B200_NORM_TWO && ctx->fuse) {  // x.x may already be known (fused epilogue / MvDot)
+    bool known = true;
+    for (int j = 0; j < k && known; ++j) {
+      int rc = 0;
+      double v = 0.0;
+      known = ctx->recall_dot(ia[j], ia[j], &v, &rc);
+      if (rc) return rc;
+      if (known) normvec[j] = std::sqrt(v);
+    }
+    if (known) {
+      ctx->dot_hits += k;
+      return 0;
+    }
+  }
   ++ctx->seq;
   for (int j = 0; j < k;) {
     const int len = run_length(j, k, mv, j);
@@ -297,8 +364,10 @@ extern "C" int b200_mv_norm(const b200_mv* mv, int type, double* normvec, int nn
     j += len;
   }
   B200_TRY(ctx->finish_reduction(k, type == B200_NORM_INF));
-  for (int j = 0; j < k; ++j)
+  for (int j = 0; j < k; ++j) {
+    if (type == B200_NORM_TWO) ctx->remember_dot(ia[j], ia[j], ctx->mbox_h[j]);
     normvec[j] = (type == B200_NORM_TWO) ? std::sqrt(ctx->mbox_h[j]) : ctx->mbox_h[j];
+  }
   return 0;
 }
 
@@ -367,18 +436,34 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
   B200_CUDA(cudaMemcpyAsync(ctx->dB, hs, bytes, cudaMemcpyHostToDevice, ctx->stream));
   B200_CUDA(cudaEventRecord(ctx->stage_ev[slot], ctx->stream));
   ctx->stage_used[slot] = true;
+  // One launch covers the whole update (A and mv both plain strided blocks)?  Then the kernel
+  // also emits x_new.x_new and x_new.x_old per column — the MvDot calls DGKS makes next.
+  FusedDots fd;
+  size_t src = 0;
+  const bool fuse = run_length(0, p, A, 0) == p && run_length(0, q, mv, 0) == q &&
+                    2 * q <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src);
+  std::vector<uint64_t> old_id(q);
+  for (int j = 0; j < q; ++j) old_id[j] = mv->id(j);
   for (int jv = 0; jv < q;) {
     const int lv = run_length(jv, q, mv, jv);
     bool first = true;
     for (int ja = 0; ja < p;) {
       const int la = run_length(ja, p, A, ja);
       B200_TRY(launch_update(ctx, mv->col(jv), mv->ld, lv, A->col(ja), A->ld, la, mv->n_local,
-                             ctx->dB + ja + (size_t)jv * p, p, alpha, first ? beta : 1.0));
+                             ctx->dB + ja + (size_t)jv * p, p, alpha, first ? beta : 1.0,
+                             fuse ? &fd : nullptr));
       first = false;
       ja += la;
     }
     jv += lv;
   }
+  mv->touch(0, q);
+  if (fuse)
+    for (int j = 0; j < q; ++j) {
+      const uint64_t nid = mv->id(j);
+      ctx->remember_dot(nid, nid, 0.0, fd.seq, src + 2 * j);
+      if (beta != 0.0) ctx->remember_dot(nid, old_id[j], 0.0, fd.seq, src + 2 * j + 1);
+    }
   return 0;
 }
 
@@ -413,6 +498,7 @@ extern "C" int b200_mv_copy_from_host(b200_mv* mv, const double* host, int64_t l
       j += len;
     }
   }
+  mv->touch(0, mv->ncols());
   B200_CUDA(cudaStreamSynchronize(ctx->stream));
   ++ctx->syncs;
   return 0;
@@ -420,6 +506,7 @@ extern "C" int b200_mv_copy_from_host(b200_mv* mv, const double* host, int64_t l
 
 extern "C" int b200_mv_device_ptr(const b200_mv* mv, int col, void** ptr, int64_t* ld) {
   if (!mv || col < 0 || col >= mv->ncols()) return fail(B200_ERR_ARG, "device_ptr: bad column");
+  mv->st->external = true;  // the caller may write through the pointer: stop tracking contents
   if (ptr) *ptr = mv->col(col);
   if (ld) *ld = mv->ld;
   return 0;
@@ -644,9 +731,15 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
     const double* xp = x->col(j);
     double* yp = y->col(j);
     if (ctx->nranks == 1 || op->peers.empty()) {
+      FusedDots fd;
+      size_t src = 0;
+      const bool fuse = len == k && k <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src);
       ctx->t_begin(K_SPMM, algo_bytes * len / k);
-      rc = launch_spmm(ctx, op, nullptr, 0, xp, x->ld, yp, y->ld, len);
+      rc = launch_spmm(ctx, op, nullptr, 0, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr);
       ctx->t_end();
+      y->touch(j, len);
+      if (fuse && !rc)
+        for (int c = 0; c < k; ++c) ctx->remember_dot(y->id(c), y->id(c), 0.0, fd.seq, src + c);
     } else {
       // grow halo buffers
       if ((size_t)len > op->buf_k) {
@@ -700,6 +793,7 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
       cudaStreamWaitEvent(ctx->stream, ctx->ev_comm, 0);
       rc = launch_spmm(ctx, op, op->bnd_rows, op->n_bnd, xp, x->ld, yp, y->ld, len);
       ctx->t_end();
+      y->touch(j, len);
     }
     j += len;
   }

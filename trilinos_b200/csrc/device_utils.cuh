@@ -57,11 +57,10 @@ __device__ __forceinline__ double warp_max(double v) {
   return v;
 }
 
-// Publish protocol for host-visible results: a thread that stored results into the mapped
-// mailbox calls fence_results() (system-scope fence, ~3 us if a whole CTA does it, so only
-// the writers do), the CTA synchronises, then one thread releases the sequence number the
-// host is spinning on.
-__device__ __forceinline__ void fence_results() { __threadfence_system(); }
+// Publish protocol for host-visible results: the threads of the finishing CTA store the results
+// into the mapped mailbox, the CTA synchronises, then ONE thread releases the sequence number the
+// host is spinning on.  st.release.sys is cumulative over the stores the barrier ordered before it,
+// so no other thread needs a system-scope fence (each one costs ~3 us of kernel tail).
 __device__ __forceinline__ void publish_flag(uint64_t* flag, uint64_t seq) {
   __syncthreads();
   if (flag != nullptr && threadIdx.x == 0) {
@@ -73,9 +72,13 @@ __device__ __forceinline__ void publish_flag(uint64_t* flag, uint64_t seq) {
 // the CTA that arrived last; the counter resets itself for the next launch.
 __device__ __forceinline__ bool last_cta_arrives(unsigned int* ticket, unsigned int total) {
   __shared__ bool is_last;
-  __threadfence();
+  // Release: the CTA barrier orders every thread's partial-sum store before thread 0's fence,
+  // and the gpu-scope fence is cumulative, so ONE fence per CTA suffices (the pattern of
+  // cooperative-groups grid.sync).  A fence in every thread cost ~8 ns per CTA, serialised
+  // GPU-wide: +15 us on a 2000-CTA kernel.
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence();
     unsigned int t = atomicAdd(ticket, 1u);
     is_last = (t == total - 1);
     if (is_last) *ticket = 0u;
@@ -83,6 +86,105 @@ __device__ __forceinline__ bool last_cta_arrives(unsigned int* ticket, unsigned 
   __syncthreads();
   if (is_last) __threadfence();
   return is_last;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Deterministic two-level folds of per-CTA partial sums.
+//
+// A single "last CTA" that walks all partials serially is latency-bound: every batch of loads
+// costs one L2 round trip (~0.4 us), and a fold over 148 ... 4000 partials took 10-20 us — as
+// long as the streaming part of a 1M-row kernel.  Here CTAs are grouped; the last CTA to finish
+// in a group folds the group's partials (one batch of independent loads), the last group to
+// finish folds the group sums.  The summation tree depends only on the launch geometry, never on
+// the arrival order, so results are run-to-run reproducible.
+//
+// tickets[0] is the global counter, tickets[1 + g] the counter of group g (all self-resetting).
+
+// E entries (few), nparts partials per entry (many): ws[e * nparts + i].  The E results of the
+// calling grid land in out[e].  `mult` = CTAs that share one partial index (gridDim.y for the
+// column reductions).  Returns true in the CTA that wrote the results.
+template <int NW, bool IS_MAX = false>
+__device__ __forceinline__ bool fold_partials_wide(double* ws, unsigned int* tickets, int E,
+                                                   int nparts, int part, int mult, double* out) {
+  constexpr int G = 64;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int ngroups = (nparts + G - 1) / G;
+  const int g = part / G;
+  const int gs = min(G, nparts - g * G);
+  if (!last_cta_arrives(&tickets[1 + g], (unsigned int)(gs * mult))) return false;
+  double* ws2 = ws + (size_t)E * nparts;
+  for (int e = warp; e < E; e += NW) {
+    const double* p = ws + (size_t)e * nparts + g * G;
+    const double a = lane < gs ? __ldcg(p + lane) : 0.0;
+    const double b = lane + 32 < gs ? __ldcg(p + lane + 32) : 0.0;
+    const double t = IS_MAX ? warp_max(fmax(a, b)) : warp_sum(a + b);
+    if (lane == 0) ws2[(size_t)e * ngroups + g] = t;
+  }
+  if (!last_cta_arrives(&tickets[0], (unsigned int)ngroups)) return false;
+  for (int e = warp; e < E; e += NW) {
+    const double* p = ws2 + (size_t)e * ngroups;
+    double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
+    for (int i = lane; i < ngroups; i += 128) {
+      const double v0 = __ldcg(p + i);
+      const double v1 = i + 32 < ngroups ? __ldcg(p + i + 32) : 0.0;
+      const double v2 = i + 64 < ngroups ? __ldcg(p + i + 64) : 0.0;
+      const double v3 = i + 96 < ngroups ? __ldcg(p + i + 96) : 0.0;
+      if (IS_MAX) {
+        t0 = fmax(t0, v0); t1 = fmax(t1, v1); t2 = fmax(t2, v2); t3 = fmax(t3, v3);
+      } else {
+        t0 += v0; t1 += v1; t2 += v2; t3 += v3;
+      }
+    }
+    const double t = IS_MAX ? warp_max(fmax(fmax(t0, t1), fmax(t2, t3)))
+                            : warp_sum((t0 + t1) + (t2 + t3));
+    if (lane == 0) out[e] = t;
+  }
+  return true;
+}
+
+// E entries (many), nparts partials per entry (<= a few hundred): ws[i * E + e] (coalesced for
+// thread-per-entry access).  store(e, sum) is called once per entry by the finishing CTA.
+template <int NT, class Store>
+__device__ __forceinline__ bool fold_partials_tall(double* ws, unsigned int* tickets, int E,
+                                                   int nparts, int part, Store store) {
+  constexpr int G = 16;
+  const int ngroups = (nparts + G - 1) / G;
+  const int g = part / G;
+  const int gs = min(G, nparts - g * G);
+  if (!last_cta_arrives(&tickets[1 + g], (unsigned int)gs)) return false;
+  double* ws2 = ws + (size_t)E * nparts;
+  for (int e = threadIdx.x; e < E; e += NT) {
+    const double* p = ws + (size_t)(g * G) * E + e;
+    double v[G];
+#pragma unroll
+    for (int i = 0; i < G; ++i) v[i] = i < gs ? __ldcg(p + (size_t)i * E) : 0.0;
+#pragma unroll
+    for (int w = 1; w < G; w <<= 1)
+#pragma unroll
+      for (int i = 0; i < G; i += 2 * w) v[i] += v[i + w];
+    ws2[(size_t)g * E + e] = v[0];
+  }
+  if (!last_cta_arrives(&tickets[0], (unsigned int)ngroups)) return false;
+  for (int e = threadIdx.x; e < E; e += NT) {
+    const double* p = ws2 + e;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int i = 0;
+    for (; i + 7 < ngroups; i += 8) {
+      const double a0 = __ldcg(p + (size_t)(i + 0) * E), a1 = __ldcg(p + (size_t)(i + 1) * E);
+      const double a2 = __ldcg(p + (size_t)(i + 2) * E), a3 = __ldcg(p + (size_t)(i + 3) * E);
+      const double a4 = __ldcg(p + (size_t)(i + 4) * E), a5 = __ldcg(p + (size_t)(i + 5) * E);
+      const double a6 = __ldcg(p + (size_t)(i + 6) * E), a7 = __ldcg(p + (size_t)(i + 7) * E);
+      s0 += a0; s1 += a1; s2 += a2; s3 += a3;
+      s0 += a4; s1 += a5; s2 += a6; s3 += a7;
+    }
+    double r[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) r[u] = i + u < ngroups ? __ldcg(p + (size_t)(i + u) * E) : 0.0;
+    s0 += r[0]; s1 += r[1]; s2 += r[2]; s3 += r[3];
+    s0 += r[4]; s1 += r[5]; s2 += r[6]; s3 += r[7];
+    store(e, (s0 + s1) + (s2 + s3));
+  }
+  return true;
 }
 
 }  // namespace b200

@@ -229,25 +229,14 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1)
     }
   }
 
-  if (!last_cta_arrives(g.ticket, gridDim.x)) return;
-  // deterministic fold over the per-CTA partials: thread = entry, fixed order over CTAs
+  // deterministic two-level fold over the per-CTA partials (thread = entry)
   const int nent = g.p * g.q;
-  const int nparts = gridDim.x;
-  for (int e = threadIdx.x; e < nent; e += NT) {
-    const double* src = g.ws + e;
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    int i = 0;
-    for (; i + 3 < nparts; i += 4) {
-      s0 += __ldcg(src + (size_t)(i + 0) * nent);
-      s1 += __ldcg(src + (size_t)(i + 1) * nent);
-      s2 += __ldcg(src + (size_t)(i + 2) * nent);
-      s3 += __ldcg(src + (size_t)(i + 3) * nent);
-    }
-    for (; i < nparts; ++i) s0 += __ldcg(src + (size_t)i * nent);
-    const int k = e / g.p, col = e % g.p;
-    g.out[(size_t)k * g.ldc + col] = g.alpha * ((s0 + s1) + (s2 + s3));
-  }
-  if (g.flag != nullptr) fence_results();
+  const bool fin = fold_partials_tall<NT>(g.ws, g.ticket, nent, (int)gridDim.x, (int)blockIdx.x,
+                                          [&](int e, double sres) {
+                                            const int k = e / g.p, col = e % g.p;
+                                            g.out[(size_t)k * g.ldc + col] = g.alpha * sres;
+                                          });
+  if (!fin) return;
   publish_flag(g.flag, g.seq);
 }
 
@@ -308,7 +297,7 @@ int launch_gram_t(Ctx* ctx, const double* A, int64_t lda, int p, const double* V
   g.alpha = alpha;
   g.ws = ctx->ws; g.ticket = ctx->ticket; g.out = out; g.ldc = ldc; g.flag = flag; g.seq = ctx->seq;
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->num_sms, g.ntiles));
-  if ((size_t)p * q * grid * sizeof(double) > kWorkspaceBytes)
+  if ((size_t)p * q * (grid + grid / 16 + 1) * sizeof(double) > kWorkspaceBytes)
     return fail(B200_ERR_ARG, "MvTransMv: partial-sum workspace too small");
   CUtensorMap tmA, tmV;
   B200_TRY(make_tmap(&tmA, A, n, p, lda, R, wfull));

@@ -69,26 +69,16 @@ __global__ void __launch_bounds__(kThreads)
     for (int w = 1; w < kWarps; ++w) t = (OP == RED_MAXABS) ? fmax(t, sm[w]) : t + sm[w];
     ws[(size_t)col * gridDim.x + blockIdx.x] = t;
   }
-  if (!last_cta_arrives(ticket, gridDim.x * gridDim.y)) return;
-  // fold the per-CTA partials: one warp per column, fixed order
-  const int ncol = gridDim.y, nparts = gridDim.x;
-  for (int c = warp; c < ncol; c += kWarps) {
-    const volatile double* p = ws + (size_t)c * nparts;
-    double t = 0.0;
-    for (int i = lane; i < nparts; i += 32) t = (OP == RED_MAXABS) ? fmax(t, p[i]) : t + p[i];
-    t = (OP == RED_MAXABS) ? warp_max(t) : warp_sum(t);
-    if (lane == 0) {
-      out[c] = t;
-      fence_results();
-    }
-  }
+  if (!fold_partials_wide<kWarps, OP == RED_MAXABS>(ws, ticket, gridDim.y, gridDim.x, blockIdx.x,
+                                                     gridDim.y, out))
+    return;
   publish_flag(flag, seq);
 }
 
 inline dim3 red_grid(int64_t n, int k) {
   const int64_t nvec = (n + 3) / 4;
   int64_t bx = (nvec + kThreads * 2 - 1) / (kThreads * 2);  // >= 2 vectors per thread
-  const int64_t cap = std::max<int64_t>(1, (int64_t)kNumSM * 8 / std::max(1, k));
+  const int64_t cap = std::max<int64_t>(1, (int64_t)kNumSM * 4 / std::max(1, k));
   if (bx > cap) bx = cap;
   if (bx < 1) bx = 1;
   return dim3((unsigned)bx, (unsigned)k, 1);
@@ -147,7 +137,6 @@ namespace {
 __global__ void publish_kernel(const double* __restrict__ src, double* __restrict__ dst, int count,
                                uint64_t* flag, uint64_t seq) {
   for (int i = threadIdx.x; i < count; i += blockDim.x) dst[i] = src[i];
-  fence_results();
   publish_flag(flag, seq);
 }
 }  // namespace

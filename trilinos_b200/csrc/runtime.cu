@@ -10,6 +10,7 @@
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace b200 {
@@ -215,6 +216,38 @@ int Ctx::wait_flag(uint64_t s) {
   return 0;
 }
 
+// ------------------------------------------------------------------ remembered dot products
+void Ctx::remember_dot(uint64_t a, uint64_t b, double val, uint64_t seq_, size_t src) {
+  if (!fuse) return;
+  if (a > b) std::swap(a, b);
+  for (int i = 0; i < kDotCache; ++i)
+    if (dots[i].a == a && dots[i].b == b) {
+      dots[i].val = val; dots[i].seq = seq_; dots[i].src = src;
+      return;
+    }
+  DotEntry& e = dots[dot_next];
+  dot_next = (dot_next + 1) % kDotCache;
+  e.a = a; e.b = b; e.val = val; e.seq = seq_; e.src = src;
+}
+
+bool Ctx::recall_dot(uint64_t a, uint64_t b, double* val, int* rc) {
+  if (!fuse) return false;
+  if (a > b) std::swap(a, b);
+  for (int i = 0; i < kDotCache; ++i) {
+    DotEntry& e = dots[i];
+    if (e.a != a || e.b != b || a == 0) continue;
+    if (e.seq != 0) {  // produced by a fused epilogue that may still be running
+      *rc = wait_flag(e.seq);
+      if (*rc) return false;
+      e.val = mbox_h[e.src];
+      e.seq = 0;
+    }
+    *val = e.val;
+    return true;
+  }
+  return false;
+}
+
 int Ctx::finish_reduction(int count, bool is_max) {
   if (nranks > 1) {
     B200_TRY(nccl_allreduce_f64(this, red_d, (size_t)count, is_max, stream));
@@ -244,6 +277,7 @@ extern "C" int b200_ctx_create(int device, b200_ctx** out) {
   B200_CUDA(cudaSetDevice(device));
   auto* c = new b200_ctx();
   c->device = device;
+  if (const char* nf = std::getenv("B200_NO_FUSE")) c->fuse = !(nf[0] == '1');
   B200_CUDA(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, device));
   B200_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   B200_CUDA(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
@@ -259,8 +293,8 @@ extern "C" int b200_ctx_create(int device, b200_ctx** out) {
   c->flag_d = (uint64_t*)dp;
   c->mbox_d = (double*)((char*)dp + 64);
   B200_CUDA(cudaMalloc((void**)&c->ws, kWorkspaceBytes));
-  B200_CUDA(cudaMalloc((void**)&c->ticket, 256));
-  B200_CUDA(cudaMemset(c->ticket, 0, 256));
+  B200_CUDA(cudaMalloc((void**)&c->ticket, kTicketBytes));
+  B200_CUDA(cudaMemset(c->ticket, 0, kTicketBytes));
   B200_CUDA(cudaMalloc((void**)&c->red_d, kMailboxDoubles * sizeof(double)));
   B200_CUDA(cudaMalloc((void**)&c->dB, kStageSlotBytes));
   B200_CUDA(cudaHostAlloc((void**)&c->stage_h, kStageSlots * kStageSlotBytes, cudaHostAllocDefault));
@@ -351,6 +385,19 @@ extern "C" int b200_ctx_counters(const b200_ctx* c, int64_t* launches, int64_t* 
   if (!c) return fail(B200_ERR_ARG, "null context");
   if (launches) *launches = c->launches;
   if (syncs) *syncs = c->syncs;
+  return 0;
+}
+
+extern "C" int b200_ctx_set_fusion(b200_ctx* c, int on) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  c->fuse = on != 0;
+  for (auto& e : c->dots) e = Ctx::DotEntry();
+  return 0;
+}
+
+extern "C" int b200_ctx_fusion_stats(const b200_ctx* c, int64_t* dot_hits) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  if (dot_hits) *dot_hits = c->dot_hits;
   return 0;
 }
 

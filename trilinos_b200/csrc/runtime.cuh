@@ -5,6 +5,7 @@
 
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
 #include <map>
 #include <memory>
@@ -19,7 +20,15 @@ constexpr int kNumSM = 148;            // B200: 2 dies x 74 SMs
 constexpr int kLdAlign = 32;           // leading dimension padded to 32 doubles (256 B)
 constexpr size_t kMailboxDoubles = 1u << 16;   // 512 KB host-mapped result mailbox
 constexpr size_t kWorkspaceBytes = 256u << 20; // per-CTA partial sums
+constexpr size_t kTicketBytes = 256u << 10;    // global + per-group arrival counters (two-level folds)
 constexpr int kStageSlots = 16;
+// Fused-reduction bookkeeping: kernels that write a column (SpMM, MvTimesMatAddMv) also emit the
+// column dot products Belos asks for next (x.x, x.x_old); the results wait in the upper part of
+// the host mailbox until the matching MvDot / MvNorm call picks them up without a launch.
+constexpr int kDotCache = 64;                   // remembered column dot products
+constexpr int kAuxSlots = 32;                   // mailbox slots for results of fused epilogues
+constexpr int kAuxSlotDoubles = 64;             // <= 32 columns x {self, with-old}
+constexpr size_t kAuxBase = kMailboxDoubles - (size_t)kAuxSlots * kAuxSlotDoubles;
 constexpr size_t kStageSlotBytes = 512u << 10; // host B blocks for MvTimesMatAddMv
 
 #define B200_CUDA(call)                                                                   \
@@ -37,6 +46,15 @@ constexpr size_t kStageSlotBytes = 512u << 10; // host B blocks for MvTimesMatAd
   } while (0)
 
 struct NcclApi;  // dlopen'ed function table (runtime.cu)
+
+// where a kernel with a fused reduction epilogue puts its column dot products
+struct FusedDots {
+  double* out = nullptr;        // device-visible mailbox slot (nullptr: no epilogue)
+  uint64_t* flag = nullptr;     // host flag, released with seq after the results are visible
+  uint64_t seq = 0;
+  double* ws = nullptr;         // per-CTA partials
+  unsigned int* ticket = nullptr;
+};
 
 enum KClass { K_SPMM = 0, K_GRAM = 1, K_UPDATE = 2, K_REDUCE = 3, K_AXPBY = 4, K_HALO = 5 };
 
@@ -71,6 +89,22 @@ struct Ctx {
   int rank = 0, nranks = 1;
   // Park-Miller state for MvRandom
   unsigned int seed = 1;
+  // content ids + remembered dot products (see kDotCache)
+  uint64_t next_id = 1;
+  struct DotEntry {
+    uint64_t a = 0, b = 0;    // content ids (a <= b)
+    double val = 0.0;
+    uint64_t seq = 0;         // 0: val is final; else: published at mbox_h[src] once flag >= seq
+    size_t src = 0;
+  };
+  DotEntry dots[kDotCache];
+  int dot_next = 0;
+  int aux_next = 0;
+  bool fuse = true;           // B200_NO_FUSE=1 disables the fused epilogues and the dot memo
+  int64_t dot_hits = 0;
+  void remember_dot(uint64_t a, uint64_t b, double val, uint64_t seq = 0, size_t src = 0);
+  // true (and *val set, waiting for the producing kernel if needed) if the product is known
+  bool recall_dot(uint64_t a, uint64_t b, double* val, int* rc);
   // counters / timing
   int64_t launches = 0, syncs = 0;
   bool timing = false;
@@ -100,7 +134,13 @@ struct Storage {
   Ctx* ctx;
   double* ptr;
   size_t bytes;
-  Storage(Ctx* c, double* p, size_t b) : ctx(c), ptr(p), bytes(b) {}
+  // content id per storage column: equal ids <=> bitwise equal columns.  Every kernel that
+  // writes a column gives it a fresh id; pure copies propagate the source id.
+  std::vector<uint64_t> ver;
+  bool external = false;  // a raw device pointer was handed out: contents are no longer tracked
+  Storage(Ctx* c, double* p, size_t b, int ncols) : ctx(c), ptr(p), bytes(b), ver((size_t)std::max(ncols, 1)) {
+    for (auto& v : ver) v = c->next_id++;
+  }
   ~Storage() { ctx->release(ptr, bytes); }
 };
 
@@ -112,6 +152,19 @@ struct MV {
   int ncols() const { return (int)cols.size(); }
   double* col(int j) const { return st->ptr + (size_t)cols[j] * ld; }
   const int* colv() const { return cols.data(); }
+  // content id of column j (a fresh one each time if the storage is not tracked)
+  uint64_t id(int j) const { return st->external ? ctx->next_id++ : st->ver[cols[j]]; }
+  void touch(int j, int len = 1) const {
+    for (int i = 0; i < len; ++i) st->ver[cols[j + i]] = ctx->next_id++;
+  }
+  void copy_id(int j, const MV* src, int js, int len = 1) const {
+    uint64_t tmp[64];
+    for (int i0 = 0; i0 < len; i0 += 64) {  // two phases: src and dst may be the same storage
+      const int m = std::min(64, len - i0);
+      for (int i = 0; i < m; ++i) tmp[i] = src->id(js + i0 + i);
+      for (int i = 0; i < m; ++i) st->ver[cols[j + i0 + i]] = tmp[i];
+    }
+  }
 };
 
 // maximal run [j, j+len) on which every listed multivector advances by exactly one
@@ -176,11 +229,14 @@ int launch_norm(Ctx*, const double* a, int64_t lda, int64_t n, int k, int type, 
 int launch_gram(Ctx*, const double* A, int64_t lda, int p, const double* V, int64_t ldv, int q,
                 int64_t n, double alpha, int out_off, int ldc, bool last);
 // update.cu : V = alpha*A*B + beta*V with B (p x q, ld = p) already in ctx->dB + boff
+// fused != nullptr: also emit {sum new^2, sum new*old} per column into fused->out[2k], [2k+1]
 int launch_update(Ctx*, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
-                  int64_t n, const double* dB, int ldb, double alpha, double beta);
+                  int64_t n, const double* dB, int ldb, double alpha, double beta,
+                  const FusedDots* fused = nullptr);
 // spmm.cu
+// fused != nullptr (single rank, stream kernel only): also emit sum y(:,k)^2 into fused->out[k]
 int launch_spmm(Ctx*, const Op* op, const int32_t* rows, int64_t nrows, const double* x,
-                int64_t ldx, double* y, int64_t ldy, int k);
+                int64_t ldx, double* y, int64_t ldy, int k, const FusedDots* fused = nullptr);
 int launch_pack(Ctx*, cudaStream_t s, const int32_t* idx, int64_t cnt, const double* x,
                 int64_t ldx, int k, double* buf);
 

@@ -23,14 +23,17 @@ namespace b200 {
 namespace {
 
 constexpr int kRows = 256;     // rows per CTA == threads per CTA
-constexpr int kCap = 4096;     // staged nonzeros per pass: 4096 * 12 B = 48 KB
+constexpr int kCap = 3968;     // staged nonzeros per pass: 3968 * 12 B = 46.5 KB (+ reduction scratch < 48 KB)
 
-template <int K>
+// FUSE: additionally emits dots[k] = sum y(:,k)^2 — the MvDot(X,X) DGKS takes of the fresh
+// Krylov block right after the apply (BelosDGKSOrthoManager.hpp:1269,1395).
+template <int K, bool FUSE>
 __global__ void __launch_bounds__(kRows)
     spmm_stream_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colind,
                        const double* __restrict__ values, int64_t n_rows, int32_t n_owned,
                        const double* __restrict__ x, int64_t ldx, const double* __restrict__ xg,
-                       int64_t ldg, double* __restrict__ y, int64_t ldy, int skip_ghost_rows) {
+                       int64_t ldg, double* __restrict__ y, int64_t ldy, int skip_ghost_rows,
+                       FusedDots fd) {
   __shared__ double sv[kCap];
   __shared__ int32_t sc[kCap];
   const int64_t r0 = (int64_t)blockIdx.x * kRows;
@@ -76,6 +79,23 @@ __global__ void __launch_bounds__(kRows)
 #pragma unroll
     for (int k = 0; k < K; ++k) y[(size_t)k * ldy + r] = acc[k];
   }
+  if (!FUSE) return;
+  __shared__ double red[kRows / 32][K];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const double t = warp_sum(r < n_rows ? acc[k] * acc[k] : 0.0);
+    if (lane == 0) red[warp][k] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x < K) {
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < kRows / 32; ++w) t += red[w][threadIdx.x];
+    fd.ws[(size_t)threadIdx.x * gridDim.x + blockIdx.x] = t;
+  }
+  if (!fold_partials_wide<kRows / 32>(fd.ws, fd.ticket, K, gridDim.x, blockIdx.x, 1, fd.out)) return;
+  publish_flag(fd.flag, fd.seq);
 }
 
 // boundary rows (explicit list): one thread per row, direct loads
@@ -117,13 +137,19 @@ __global__ void __launch_bounds__(256)
 
 template <int K>
 int spmm_t(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, const double* x,
-           int64_t ldx, const double* xg, int64_t ldg, double* y, int64_t ldy, int skip) {
+           int64_t ldx, const double* xg, int64_t ldg, double* y, int64_t ldy, int skip,
+           const FusedDots& fd) {
   if (rows == nullptr) {
     const unsigned grid = (unsigned)((op->n_local + kRows - 1) / kRows);
     if (grid == 0) return 0;
-    spmm_stream_kernel<K><<<grid, kRows, 0, ctx->stream>>>(op->rowptr, op->colind, op->values,
-                                                            op->n_local, (int32_t)op->n_local, x,
-                                                            ldx, xg, ldg, y, ldy, skip);
+    if (fd.out)
+      spmm_stream_kernel<K, true><<<grid, kRows, 0, ctx->stream>>>(
+          op->rowptr, op->colind, op->values, op->n_local, (int32_t)op->n_local, x, ldx, xg, ldg,
+          y, ldy, skip, fd);
+    else
+      spmm_stream_kernel<K, false><<<grid, kRows, 0, ctx->stream>>>(
+          op->rowptr, op->colind, op->values, op->n_local, (int32_t)op->n_local, x, ldx, xg, ldg,
+          y, ldy, skip, fd);
   } else {
     if (nrows == 0) return 0;
     const unsigned grid = (unsigned)((nrows + 255) / 256);
@@ -141,7 +167,7 @@ int spmm_t(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, const dou
 // rows == nullptr: stream kernel over all local rows (skipping ghost rows when the operator has
 // ghosts and the caller asked for the interior pass via nrows == -1); otherwise the row list.
 int launch_spmm(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, const double* x,
-                int64_t ldx, double* y, int64_t ldy, int k) {
+                int64_t ldx, double* y, int64_t ldy, int k, const FusedDots* fused) {
   const int skip = (rows == nullptr && nrows == -1) ? 1 : 0;
   const double* xg = op->recv_buf;
   const int64_t ldg = op->n_ghost;  // ghost block is stored densely per right-hand side
@@ -154,11 +180,17 @@ int launch_spmm(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, cons
     const double* xgk = xg ? xg + (size_t)k0 * ldg : nullptr;
     double* yk = y + (size_t)k0 * ldy;
     int rc;
+    FusedDots fd;
+    if (fused && fused->out && rows == nullptr && !skip) {
+      fd = *fused;
+      fd.out = fused->out + k0;
+      if (k0 + step < k) fd.flag = nullptr;
+    }
     switch (step) {
-      case 8: rc = spmm_t<8>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip); break;
-      case 4: rc = spmm_t<4>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip); break;
-      case 2: rc = spmm_t<2>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip); break;
-      default: rc = spmm_t<1>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip); break;
+      case 8: rc = spmm_t<8>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip, fd); break;
+      case 4: rc = spmm_t<4>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip, fd); break;
+      case 2: rc = spmm_t<2>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip, fd); break;
+      default: rc = spmm_t<1>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip, fd); break;
     }
     if (rc) return rc;
     k0 += step;

@@ -22,11 +22,15 @@ namespace {
 constexpr int kThreads = 128;
 constexpr int kPChunk = 256;  // rows of B per shared-memory stage
 
-template <int Q, int UNR>
+// FUSE: the kernel additionally emits, per output column k, dots[2k] = sum new(:,k)^2 and
+// dots[2k+1] = sum new(:,k)*old(:,k) (old = V before the update; only when beta != 0) — the two
+// inner products DGKS asks for right after the update (BelosDGKSOrthoManager.hpp:1091,1128,1480),
+// so those MvDot calls need neither a launch nor another pass over the column.
+template <int Q, int UNR, bool FUSE>
 __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
     update_kernel(double* __restrict__ V, int64_t ldv, const double* __restrict__ A, int64_t lda,
                   int p, int64_t n, const double* __restrict__ B, int ldb, double alpha,
-                  double beta) {
+                  double beta, FusedDots fd) {
   __shared__ double Bs[kPChunk][Q];
   const int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
   const bool active = r < n;
@@ -76,32 +80,79 @@ __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
       }
     }
   }
-  if (!active) return;
+  if (!FUSE && !active) return;
+  double dself[Q], dold[Q];
 #pragma unroll
   for (int k = 0; k < Q; ++k) {
-    double* vp = V + (size_t)k * ldv + r;
-    double4v o;
-    if (beta == 0.0) {
-      o.x = alpha * acc[0][k]; o.y = alpha * acc[1][k];
-      o.z = alpha * acc[2][k]; o.w = alpha * acc[3][k];
-    } else {
-      const double4v v = ld_plain4(vp);
-      o.x = fma(alpha, acc[0][k], beta * v.x);
-      o.y = fma(alpha, acc[1][k], beta * v.y);
-      o.z = fma(alpha, acc[2][k], beta * v.z);
-      o.w = fma(alpha, acc[3][k], beta * v.w);
-    }
-    st_plain4(vp, o);
+    dself[k] = 0.0;
+    dold[k] = 0.0;
   }
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < Q; ++k) {
+      double* vp = V + (size_t)k * ldv + r;
+      double4v o, v{0.0, 0.0, 0.0, 0.0};
+      if (beta == 0.0) {
+        o.x = alpha * acc[0][k]; o.y = alpha * acc[1][k];
+        o.z = alpha * acc[2][k]; o.w = alpha * acc[3][k];
+      } else {
+        v = ld_plain4(vp);
+        o.x = fma(alpha, acc[0][k], beta * v.x);
+        o.y = fma(alpha, acc[1][k], beta * v.y);
+        o.z = fma(alpha, acc[2][k], beta * v.z);
+        o.w = fma(alpha, acc[3][k], beta * v.w);
+      }
+      st_plain4(vp, o);
+      if (FUSE) {
+        // rows >= n of the last 4-vector are padding and must not enter the sums
+        const bool m1 = r + 1 < n, m2 = r + 2 < n, m3 = r + 3 < n;
+        double s0 = o.x * o.x, s1 = m1 ? o.y * o.y : 0.0;
+        s0 = m2 ? fma(o.z, o.z, s0) : s0;
+        s1 = m3 ? fma(o.w, o.w, s1) : s1;
+        dself[k] = s0 + s1;
+        double t0 = o.x * v.x, t1 = m1 ? o.y * v.y : 0.0;
+        t0 = m2 ? fma(o.z, v.z, t0) : t0;
+        t1 = m3 ? fma(o.w, v.w, t1) : t1;
+        dold[k] = t0 + t1;
+      }
+    }
+  }
+  if (!FUSE) return;
+  // CTA partials -> workspace [entry][cta]; the CTA that arrives last folds them in a fixed order
+  __shared__ double red[kThreads / 32][2 * Q];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < Q; ++k) {
+    const double a = warp_sum(dself[k]), b = warp_sum(dold[k]);
+    if (lane == 0) {
+      red[warp][2 * k] = a;
+      red[warp][2 * k + 1] = b;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 * Q) {
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) t += red[w][threadIdx.x];
+    fd.ws[(size_t)threadIdx.x * gridDim.x + blockIdx.x] = t;
+  }
+  if (!fold_partials_wide<kThreads / 32>(fd.ws, fd.ticket, 2 * Q, gridDim.x, blockIdx.x, 1, fd.out))
+    return;
+  publish_flag(fd.flag, fd.seq);
 }
 
 template <int Q, int UNR>
 int launch_update_t(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_t lda, int p,
-                    int64_t n, const double* dB, int ldb, double alpha, double beta) {
+                    int64_t n, const double* dB, int ldb, double alpha, double beta,
+                    const FusedDots& fd) {
   const int64_t nthr = (n + 3) / 4;
   const unsigned grid = (unsigned)((nthr + kThreads - 1) / kThreads);
-  update_kernel<Q, UNR><<<grid, kThreads, 0, ctx->stream>>>(V, ldv, A, lda, p, n, dB, ldb, alpha,
-                                                             beta);
+  if (fd.out)
+    update_kernel<Q, UNR, true><<<grid, kThreads, 0, ctx->stream>>>(V, ldv, A, lda, p, n, dB, ldb,
+                                                                     alpha, beta, fd);
+  else
+    update_kernel<Q, UNR, false><<<grid, kThreads, 0, ctx->stream>>>(V, ldv, A, lda, p, n, dB,
+                                                                      ldb, alpha, beta, fd);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
   return 0;
@@ -110,7 +161,8 @@ int launch_update_t(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_t l
 }  // namespace
 
 int launch_update(Ctx* ctx, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
-                  int64_t n, const double* dB, int ldb, double alpha, double beta) {
+                  int64_t n, const double* dB, int ldb, double alpha, double beta,
+                  const FusedDots* fused) {
   if (n <= 0 || q <= 0) return 0;
   ctx->t_begin(K_UPDATE, 8.0 * n * ((double)p + (beta == 0.0 ? 1.0 : 2.0) * q));
   int k0 = 0, rc = 0;
@@ -120,11 +172,17 @@ int launch_update(Ctx* ctx, double* V, int64_t ldv, int q, const double* A, int6
     const double* Bk = dB + (size_t)k0 * ldb;
     int step;
     if (rem >= 8) step = 8; else if (rem >= 4) step = 4; else if (rem >= 2) step = 2; else step = 1;
+    FusedDots fd;
+    if (fused && fused->out) {
+      fd = *fused;
+      fd.out = fused->out + 2 * k0;
+      if (k0 + step < q) fd.flag = nullptr;  // only the last launch releases the sequence number
+    }
     switch (step) {
-      case 8: rc = launch_update_t<8, 4>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta); break;
-      case 4: rc = launch_update_t<4, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta); break;
-      case 2: rc = launch_update_t<2, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta); break;
-      default: rc = launch_update_t<1, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta); break;
+      case 8: rc = launch_update_t<8, 4>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
+      case 4: rc = launch_update_t<4, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
+      case 2: rc = launch_update_t<2, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
+      default: rc = launch_update_t<1, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
     }
     k0 += step;
   }
