@@ -23,7 +23,7 @@ namespace b200 {
 namespace {
 
 constexpr int kRows = 256;     // rows per CTA == threads per CTA
-constexpr int kCap = 3968;     // staged nonzeros per pass: 3968 * 12 B = 46.5 KB (+ reduction scratch < 48 KB)
+constexpr int kCap = 4064;     // staged nonzeros per pass: 4064 * 12 B = 47.6 KB (+ ticket flag < 48 KB)
 
 // FUSE: additionally emits dots[k] = sum y(:,k)^2 — the MvDot(X,X) DGKS takes of the fresh
 // Krylov block right after the apply (BelosDGKSOrthoManager.hpp:1269,1395).
@@ -36,55 +36,68 @@ __global__ void __launch_bounds__(kRows)
                        FusedDots fd) {
   __shared__ double sv[kCap];
   __shared__ int32_t sc[kCap];
-  const int64_t r0 = (int64_t)blockIdx.x * kRows;
-  const int64_t r = r0 + threadIdx.x;
-  const int64_t rl = min(r0 + (int64_t)kRows, n_rows);
-  const int32_t seg_b = rowptr[r0], seg_e = rowptr[rl];
-  int32_t my_b = 0, my_e = 0;
-  if (r < n_rows) {
-    my_b = rowptr[r];
-    my_e = rowptr[r + 1];
-  }
-  double acc[K];
+  // persistent CTAs walk the 256-row tiles round-robin (see update.cu: the fused reduction's
+  // fence + ticket round trip is then paid once per CTA, not once per wave of CTAs)
+  const int64_t ntiles = (n_rows + kRows - 1) / kRows;
+  double ss[K];
 #pragma unroll
-  for (int k = 0; k < K; ++k) acc[k] = 0.0;
-  bool has_ghost = false;
+  for (int k = 0; k < K; ++k) ss[k] = 0.0;
 
-  for (int32_t base = seg_b; base < seg_e; base += kCap) {
-    const int32_t cnt = min(kCap, seg_e - base);
-    __syncthreads();
-    for (int32_t i = threadIdx.x; i < cnt; i += kRows) {
-      sv[i] = ld_stream1(values + base + i);
-      sc[i] = __ldg(colind + base + i);
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t r0 = tile * kRows;
+    const int64_t r = r0 + threadIdx.x;
+    const int64_t rl = min(r0 + (int64_t)kRows, n_rows);
+    const int32_t seg_b = rowptr[r0], seg_e = rowptr[rl];
+    int32_t my_b = 0, my_e = 0;
+    if (r < n_rows) {
+      my_b = rowptr[r];
+      my_e = rowptr[r + 1];
     }
-    __syncthreads();
-    const int32_t lo = max(my_b, base), hi = min(my_e, base + cnt);
-    for (int32_t e = lo; e < hi; ++e) {
-      const double v = sv[e - base];
-      const int32_t c = sc[e - base];
-      if (c < n_owned) {
+    double acc[K];
 #pragma unroll
-        for (int k = 0; k < K; ++k) acc[k] = fma(v, __ldg(x + (size_t)k * ldx + c), acc[k]);
-      } else {
-        has_ghost = true;
-        if (!skip_ghost_rows) {
+    for (int k = 0; k < K; ++k) acc[k] = 0.0;
+    bool has_ghost = false;
+
+    for (int32_t base = seg_b; base < seg_e; base += kCap) {
+      const int32_t cnt = min(kCap, seg_e - base);
+      __syncthreads();
+      for (int32_t i = threadIdx.x; i < cnt; i += kRows) {
+        sv[i] = ld_stream1(values + base + i);
+        sc[i] = __ldg(colind + base + i);
+      }
+      __syncthreads();
+      const int32_t lo = max(my_b, base), hi = min(my_e, base + cnt);
+      for (int32_t e = lo; e < hi; ++e) {
+        const double v = sv[e - base];
+        const int32_t c = sc[e - base];
+        if (c < n_owned) {
 #pragma unroll
-          for (int k = 0; k < K; ++k)
-            acc[k] = fma(v, __ldg(xg + (size_t)k * ldg + (c - n_owned)), acc[k]);
+          for (int k = 0; k < K; ++k) acc[k] = fma(v, __ldg(x + (size_t)k * ldx + c), acc[k]);
+        } else {
+          has_ghost = true;
+          if (!skip_ghost_rows) {
+#pragma unroll
+            for (int k = 0; k < K; ++k)
+              acc[k] = fma(v, __ldg(xg + (size_t)k * ldg + (c - n_owned)), acc[k]);
+          }
         }
       }
     }
-  }
-  if (r < n_rows && !(skip_ghost_rows && has_ghost)) {
+    if (r < n_rows && !(skip_ghost_rows && has_ghost)) {
 #pragma unroll
-    for (int k = 0; k < K; ++k) y[(size_t)k * ldy + r] = acc[k];
+      for (int k = 0; k < K; ++k) {
+        y[(size_t)k * ldy + r] = acc[k];
+        if (FUSE) ss[k] = fma(acc[k], acc[k], ss[k]);
+      }
+    }
   }
   if (!FUSE) return;
-  __shared__ double red[kRows / 32][K];
+  __syncthreads();  // sv is reused as reduction scratch
+  double(*red)[K] = reinterpret_cast<double(*)[K]>(sv);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int k = 0; k < K; ++k) {
-    const double t = warp_sum(r < n_rows ? acc[k] * acc[k] : 0.0);
+    const double t = warp_sum(ss[k]);
     if (lane == 0) red[warp][k] = t;
   }
   __syncthreads();
@@ -140,8 +153,15 @@ int spmm_t(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, const dou
            int64_t ldx, const double* xg, int64_t ldg, double* y, int64_t ldy, int skip,
            const FusedDots& fd) {
   if (rows == nullptr) {
-    const unsigned grid = (unsigned)((op->n_local + kRows - 1) / kRows);
-    if (grid == 0) return 0;
+    const int64_t ntiles = (op->n_local + kRows - 1) / kRows;
+    if (ntiles == 0) return 0;
+    static int per_sm = 0;  // resident CTAs per SM of this instantiation
+    if (per_sm == 0) {
+      B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spmm_stream_kernel<K, true>,
+                                                              kRows, 0));
+      per_sm = std::max(per_sm, 1);
+    }
+    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)ctx->num_sms * per_sm);
     if (fd.out)
       spmm_stream_kernel<K, true><<<grid, kRows, 0, ctx->stream>>>(
           op->rowptr, op->colind, op->values, op->n_local, (int32_t)op->n_local, x, ldx, xg, ldg,

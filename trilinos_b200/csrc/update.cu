@@ -32,93 +32,108 @@ __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
                   int p, int64_t n, const double* __restrict__ B, int ldb, double alpha,
                   double beta, FusedDots fd) {
   __shared__ double Bs[kPChunk][Q];
-  const int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
-  const bool active = r < n;
-  const double* Ar = A + (active ? r : 0);
-  double acc[4][Q];
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int k = 0; k < Q; ++k) acc[i][k] = 0.0;
-
-  for (int j0 = 0; j0 < p; j0 += kPChunk) {
-    const int pc = min(kPChunk, p - j0);
-    __syncthreads();
-    for (int e = threadIdx.x; e < pc * Q; e += kThreads) {
-      const int k = e / pc, j = e % pc;  // coalesced read of column k of B
-      Bs[j][k] = B[(size_t)k * ldb + j0 + j];
-    }
-    __syncthreads();
-    if (active) {
-      const double* Aj = Ar + (size_t)j0 * lda;
-      int j = 0;
-      for (; j + UNR <= pc; j += UNR) {
-        double4v a[UNR];
-#pragma unroll
-        for (int u = 0; u < UNR; ++u) a[u] = ld_stream4(Aj + (size_t)(j + u) * lda);
-#pragma unroll
-        for (int u = 0; u < UNR; ++u)
-#pragma unroll
-          for (int k = 0; k < Q; ++k) {
-            const double b = Bs[j + u][k];
-            acc[0][k] = fma(a[u].x, b, acc[0][k]);
-            acc[1][k] = fma(a[u].y, b, acc[1][k]);
-            acc[2][k] = fma(a[u].z, b, acc[2][k]);
-            acc[3][k] = fma(a[u].w, b, acc[3][k]);
-          }
-      }
-      for (; j < pc; ++j) {
-        const double4v a = ld_stream4(Aj + (size_t)j * lda);
-#pragma unroll
-        for (int k = 0; k < Q; ++k) {
-          const double b = Bs[j][k];
-          acc[0][k] = fma(a.x, b, acc[0][k]);
-          acc[1][k] = fma(a.y, b, acc[1][k]);
-          acc[2][k] = fma(a.z, b, acc[2][k]);
-          acc[3][k] = fma(a.w, b, acc[3][k]);
-        }
-      }
-    }
-  }
-  if (!FUSE && !active) return;
+  // Persistent CTAs (grid = resident capacity) walk the 512-row tiles round-robin: the fused
+  // reduction's fence + ticket round trip (~2 us during which the CTA streams nothing) is paid
+  // once per CTA instead of once per wave of CTAs.
+  const int64_t ntiles = (n + 4 * kThreads - 1) / (4 * kThreads);
+  const bool single = p <= kPChunk;  // B fits one stage: load it once for all tiles
   double dself[Q], dold[Q];
 #pragma unroll
   for (int k = 0; k < Q; ++k) {
     dself[k] = 0.0;
     dold[k] = 0.0;
   }
-  if (active) {
+  auto stage = [&](int j0, int pc) {
+    for (int e = threadIdx.x; e < pc * Q; e += kThreads) {
+      const int k = e / pc, j = e % pc;  // coalesced read of column k of B
+      Bs[j][k] = B[(size_t)k * ldb + j0 + j];
+    }
+  };
+  if (single) {
+    stage(0, p);
+    __syncthreads();
+  }
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t r = (tile * kThreads + threadIdx.x) * 4;
+    const bool active = r < n;
+    const double* Ar = A + (active ? r : 0);
+    double acc[4][Q];
 #pragma unroll
-    for (int k = 0; k < Q; ++k) {
-      double* vp = V + (size_t)k * ldv + r;
-      double4v o, v{0.0, 0.0, 0.0, 0.0};
-      if (beta == 0.0) {
-        o.x = alpha * acc[0][k]; o.y = alpha * acc[1][k];
-        o.z = alpha * acc[2][k]; o.w = alpha * acc[3][k];
-      } else {
-        v = ld_plain4(vp);
-        o.x = fma(alpha, acc[0][k], beta * v.x);
-        o.y = fma(alpha, acc[1][k], beta * v.y);
-        o.z = fma(alpha, acc[2][k], beta * v.z);
-        o.w = fma(alpha, acc[3][k], beta * v.w);
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int k = 0; k < Q; ++k) acc[i][k] = 0.0;
+
+    for (int j0 = 0; j0 < p; j0 += kPChunk) {
+      const int pc = min(kPChunk, p - j0);
+      if (!single) {
+        __syncthreads();
+        stage(j0, pc);
+        __syncthreads();
       }
-      st_plain4(vp, o);
-      if (FUSE) {
-        // rows >= n of the last 4-vector are padding and must not enter the sums
-        const bool m1 = r + 1 < n, m2 = r + 2 < n, m3 = r + 3 < n;
-        double s0 = o.x * o.x, s1 = m1 ? o.y * o.y : 0.0;
-        s0 = m2 ? fma(o.z, o.z, s0) : s0;
-        s1 = m3 ? fma(o.w, o.w, s1) : s1;
-        dself[k] = s0 + s1;
-        double t0 = o.x * v.x, t1 = m1 ? o.y * v.y : 0.0;
-        t0 = m2 ? fma(o.z, v.z, t0) : t0;
-        t1 = m3 ? fma(o.w, v.w, t1) : t1;
-        dold[k] = t0 + t1;
+      if (active) {
+        const double* Aj = Ar + (size_t)j0 * lda;
+        int j = 0;
+        for (; j + UNR <= pc; j += UNR) {
+          double4v a[UNR];
+#pragma unroll
+          for (int u = 0; u < UNR; ++u) a[u] = ld_stream4(Aj + (size_t)(j + u) * lda);
+#pragma unroll
+          for (int u = 0; u < UNR; ++u)
+#pragma unroll
+            for (int k = 0; k < Q; ++k) {
+              const double b = Bs[j + u][k];
+              acc[0][k] = fma(a[u].x, b, acc[0][k]);
+              acc[1][k] = fma(a[u].y, b, acc[1][k]);
+              acc[2][k] = fma(a[u].z, b, acc[2][k]);
+              acc[3][k] = fma(a[u].w, b, acc[3][k]);
+            }
+        }
+        for (; j < pc; ++j) {
+          const double4v a = ld_stream4(Aj + (size_t)j * lda);
+#pragma unroll
+          for (int k = 0; k < Q; ++k) {
+            const double b = Bs[j][k];
+            acc[0][k] = fma(a.x, b, acc[0][k]);
+            acc[1][k] = fma(a.y, b, acc[1][k]);
+            acc[2][k] = fma(a.z, b, acc[2][k]);
+            acc[3][k] = fma(a.w, b, acc[3][k]);
+          }
+        }
+      }
+    }
+    if (active) {
+#pragma unroll
+      for (int k = 0; k < Q; ++k) {
+        double* vp = V + (size_t)k * ldv + r;
+        double4v o, v{0.0, 0.0, 0.0, 0.0};
+        if (beta == 0.0) {
+          o.x = alpha * acc[0][k]; o.y = alpha * acc[1][k];
+          o.z = alpha * acc[2][k]; o.w = alpha * acc[3][k];
+        } else {
+          v = ld_plain4(vp);
+          o.x = fma(alpha, acc[0][k], beta * v.x);
+          o.y = fma(alpha, acc[1][k], beta * v.y);
+          o.z = fma(alpha, acc[2][k], beta * v.z);
+          o.w = fma(alpha, acc[3][k], beta * v.w);
+        }
+        st_plain4(vp, o);
+        if (FUSE) {
+          // rows >= n of the last 4-vector are padding and must not enter the sums
+          const bool m1 = r + 1 < n, m2 = r + 2 < n, m3 = r + 3 < n;
+          double s0 = o.x * o.x, s1 = m1 ? o.y * o.y : 0.0;
+          s0 = m2 ? fma(o.z, o.z, s0) : s0;
+          s1 = m3 ? fma(o.w, o.w, s1) : s1;
+          dself[k] += s0 + s1;
+          double t0 = o.x * v.x, t1 = m1 ? o.y * v.y : 0.0;
+          t0 = m2 ? fma(o.z, v.z, t0) : t0;
+          t1 = m3 ? fma(o.w, v.w, t1) : t1;
+          dold[k] += t0 + t1;
+        }
       }
     }
   }
   if (!FUSE) return;
-  // CTA partials -> workspace [entry][cta]; the CTA that arrives last folds them in a fixed order
+  // CTA partials -> workspace [entry][cta]; two-level deterministic fold, last CTA publishes
   __shared__ double red[kThreads / 32][2 * Q];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -145,8 +160,14 @@ template <int Q, int UNR>
 int launch_update_t(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_t lda, int p,
                     int64_t n, const double* dB, int ldb, double alpha, double beta,
                     const FusedDots& fd) {
-  const int64_t nthr = (n + 3) / 4;
-  const unsigned grid = (unsigned)((nthr + kThreads - 1) / kThreads);
+  const int64_t ntiles = (n + 4 * kThreads - 1) / (4 * kThreads);
+  static int per_sm = 0;  // resident CTAs per SM of this instantiation
+  if (per_sm == 0) {
+    B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, update_kernel<Q, UNR, true>,
+                                                            kThreads, 0));
+    per_sm = std::max(per_sm, 1);
+  }
+  const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)ctx->num_sms * per_sm);
   if (fd.out)
     update_kernel<Q, UNR, true><<<grid, kThreads, 0, ctx->stream>>>(V, ldv, A, lda, p, n, dB, ldb,
                                                                      alpha, beta, fd);
