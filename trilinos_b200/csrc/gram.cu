@@ -69,13 +69,27 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 // 2-D TMA tensor copy global -> shared (coordinates: c0 = row, c1 = column), completion on an
 // mbarrier (SASS: UTMALDG)
+// `policy`: L2 eviction policy (createpolicy).  The basis A is touched once per call -> evict_first;
+// the block V is re-read once per 32-column block of A -> evict_last.  Without the hints the A
+// stream pushed V out of L2 and V came back from DRAM every column block (ncu: 924 MB read for
+// 832 algorithmic MB at p = 100, q = 4).
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* tmap, int c0, int c1,
-                                            uint64_t* bar) {
+                                            uint64_t* bar, uint64_t policy) {
   asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3}], [%4], %5;" ::
           "r"(smem_u32(dst)),
-      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(c0), "r"(c1), "r"(smem_u32(bar)), "l"(policy)
       : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
 }
 __device__ __forceinline__ double2 lds128(uint32_t addr) {
   double2 v;
@@ -144,6 +158,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1)
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
+      const uint64_t pol_a = l2_policy_evict_first();
+      const uint64_t pol_v = l2_policy_evict_last();  // V is also the next kernel's operand
       for (int cb = 0; cb < ncb; ++cb) {
         const int col0 = cb * kTC;
         for (int t = 0; t < ntile_cta; ++t) {
@@ -151,8 +167,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1)
           const int r0 = (int)((t_begin + t) * R);
           unsigned char* st = stage0 + (size_t)s * stage_bytes;
           mbar_expect_tx(&full_bar[s], stage_bytes);
-          tma_load_2d(st, &tmA, r0, col0, &full_bar[s]);
-          tma_load_2d(st + (size_t)wfull * R * 8, &tmV, r0, 0, &full_bar[s]);
+          tma_load_2d(st, &tmA, r0, col0, &full_bar[s], pol_a);
+          tma_load_2d(st + (size_t)wfull * R * 8, &tmV, r0, 0, &full_bar[s], pol_v);
           if (++s == g.nstage) { s = 0; ph ^= 1u; }
         }
       }
