@@ -518,8 +518,10 @@ namespace {
 template <class T>
 int upload(T** dst, const std::vector<T>& src) {
   *dst = nullptr;
-  const size_t bytes = std::max<size_t>(src.size(), 1) * sizeof(T);
+  // 512 B of zeroed slack: the SpMM bulk copies round segment ends up to 256-B multiples
+  const size_t bytes = src.size() * sizeof(T) + 512;
   B200_CUDA(cudaMalloc((void**)dst, bytes));
+  B200_CUDA(cudaMemset(*dst, 0, bytes));
   if (!src.empty())
     B200_CUDA(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
   return 0;
@@ -595,6 +597,13 @@ extern "C" int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_b
   op->n_ghost = n_ghost;
   op->nnz = nnz;
   op->max_row_nnz = max_row;
+  for (int i = 0; i < 3; ++i) {
+    const int64_t R = 64 << i;
+    int64_t m = 0;
+    for (int64_t r0 = 0; r0 < n_local; r0 += R)
+      m = std::max<int64_t>(m, rp[std::min(r0 + R, n_local)] - rp[r0]);
+    op->max_tile_nnz[i] = m;
+  }
   op->n_bnd = (int64_t)bnd.size();
   int rc = upload(&op->rowptr, rp);
   if (!rc) rc = upload(&op->colind, col_local);

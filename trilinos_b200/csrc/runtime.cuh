@@ -209,6 +209,8 @@ struct Op {
   double* recv_buf = nullptr;
   size_t buf_k = 0;
   int max_row_nnz = 0;
+  // largest nonzero count of any tile of 64 / 128 / 256 consecutive rows (SpMM stage sizing)
+  int64_t max_tile_nnz[3] = {0, 0, 0};
 };
 
 // ---- kernel launchers (defined in the .cu files) ---------------------------------

@@ -18,96 +18,248 @@
 #include "device_utils.cuh"
 #include "runtime.cuh"
 
+#include <cstdlib>
+
 namespace b200 {
 
 namespace {
 
-constexpr int kRows = 256;     // rows per CTA == threads per CTA
-constexpr int kCap = 4064;     // staged nonzeros per pass: 4064 * 12 B = 47.6 KB (+ ticket flag < 48 KB)
+constexpr int kThreadsC = 256;      // consumer threads per CTA
+constexpr int kNWC = kThreadsC / 32;  // consumer warps
+constexpr int kCapMax = 8184;       // largest stage capacity (nonzeros); larger tiles are chunked
+constexpr int kMaxStagesSpmm = 4;
+constexpr int kSlack = 96;          // stage slots beyond cap: 128-B alignment of both copies' source
+                                    // (<= 31 before, <= 31 after) + batch over-read (7); keeps
+                                    // (cap + kSlack) a multiple of 32 so every segment is 128-B aligned
+constexpr size_t kSpmmSmemBudget = 200u << 10;  // per SM, all resident CTAs
 
-// FUSE: additionally emits dots[k] = sum y(:,k)^2 — the MvDot(X,X) DGKS takes of the fresh
+enum SpmmMode { SPMM_PLAIN = 0, SPMM_FUSE = 1, SPMM_GHOST = 2 };
+
+struct SpmmGeom {
+  int cap;          // nonzeros per stage (multiple of 4)
+  int stage_bytes;  // (cap + kSlack) * 12 + (R + 4) * 4, rounded up to 128
+  int nstage;
+};
+
+// Persistent TMA-streamed CSR kernel.
+//  * A CTA owns a contiguous range of R-row tiles (R = 256 / T), so the x gather of neighbouring
+//    tiles re-uses L1/L2 lines.  One producer thread streams each tile's values / column indices /
+//    row pointers -- three contiguous segments -- into a shared-memory ring with 1-D bulk copies
+//    (cp.async.bulk, completion on an mbarrier), several tiles ahead of the 8 consumer warps: the
+//    HBM stream never waits for the gather phase.
+//  * Consumer thread t works on row r0 + (t mod R) for the K/T right-hand sides of group t / R
+//    (T > 1 for long rows: a tile then still fits one stage and all 256 threads stay busy).  Each
+//    row is reduced left to right, the reference's order, for every right-hand side.
+//  * The gathers of U consecutive nonzeros x K/T right-hand sides (16 loads) are issued before
+//    the first FMA needs one: the gather is latency-, not bandwidth-limited.
+//  * Tiles with more than `cap` nonzeros take several stages ("chunks"); a thread only touches the
+//    part of its row that lies in the current chunk.
+// SPMM_FUSE: additionally emits dots[k] = sum y(:,k)^2 -- the MvDot(X,X) DGKS takes of the fresh
 // Krylov block right after the apply (BelosDGKSOrthoManager.hpp:1269,1395).
-template <int K, bool FUSE>
-__global__ void __launch_bounds__(kRows)
+// SPMM_GHOST: columns >= n_owned come from the halo buffer xg; with skip_ghost_rows the rows that
+// touch one are left to the boundary kernel (they are computed here too, but not stored).
+template <int K, int T, int MODE>
+__global__ void __launch_bounds__(kThreadsC + 32, 3)
     spmm_stream_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colind,
                        const double* __restrict__ values, int64_t n_rows, int32_t n_owned,
                        const double* __restrict__ x, int64_t ldx, const double* __restrict__ xg,
                        int64_t ldg, double* __restrict__ y, int64_t ldy, int skip_ghost_rows,
-                       FusedDots fd) {
-  __shared__ double sv[kCap];
-  __shared__ int32_t sc[kCap];
-  // persistent CTAs walk the 256-row tiles round-robin (see update.cu: the fused reduction's
-  // fence + ticket round trip is then paid once per CTA, not once per wave of CTAs)
-  const int64_t ntiles = (n_rows + kRows - 1) / kRows;
-  double ss[K];
-#pragma unroll
-  for (int k = 0; k < K; ++k) ss[k] = 0.0;
+                       SpmmGeom g, FusedDots fd) {
+  constexpr int R = kThreadsC / T;   // rows per tile
+  constexpr int KT = K / T;          // right-hand sides per thread
+  constexpr int U = KT >= 8 ? 2 : KT >= 4 ? 4 : 8;  // nonzeros per gather batch
+  constexpr int kRp = R + 4;         // row-pointer slice (R + 1 entries, 16-B multiple)
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint64_t full_bar[kMaxStagesSpmm], empty_bar[kMaxStagesSpmm];
+  __shared__ double red[kNWC][KT];
+  // (indexing smem_raw directly keeps the accesses in the shared address space: LDS with folded
+  // immediates instead of generic loads; 16-B alignment is all the bulk copies need)
+  unsigned char* const stage0 = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t ntiles = (n_rows + R - 1) / R;
+  const int64_t t_begin = ntiles * blockIdx.x / gridDim.x;
+  const int64_t t_end = ntiles * (blockIdx.x + 1) / gridDim.x;
+  const uint32_t off_c = (uint32_t)(g.cap + kSlack) * 8u, off_rp = (uint32_t)(g.cap + kSlack) * 12u;
 
-  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const int64_t r0 = tile * kRows;
-    const int64_t r = r0 + threadIdx.x;
-    const int64_t rl = min(r0 + (int64_t)kRows, n_rows);
-    const int32_t seg_b = rowptr[r0], seg_e = rowptr[rl];
-    int32_t my_b = 0, my_e = 0;
-    if (r < n_rows) {
-      my_b = rowptr[r];
-      my_e = rowptr[r + 1];
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < g.nstage; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], kNWC);
     }
-    double acc[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) acc[k] = 0.0;
-    bool has_ghost = false;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
 
-    for (int32_t base = seg_b; base < seg_e; base += kCap) {
-      const int32_t cnt = min(kCap, seg_e - base);
-      __syncthreads();
-      for (int32_t i = threadIdx.x; i < cnt; i += kRows) {
-        sv[i] = ld_stream1(values + base + i);
-        sc[i] = __ldg(colind + base + i);
+  double ss[KT];
+#pragma unroll
+  for (int k = 0; k < KT; ++k) ss[k] = 0.0;
+
+  if (warp == kNWC) {
+    // ---------------------------------------------------------------- producer warp
+    // all lanes fetch the segment bounds of 32 tiles at a time; lane 0 issues the copies
+    int s = 0;
+    uint32_t ph = 0;
+    const uint64_t pol = l2_policy_evict_first();  // the matrix is streamed once per apply
+    // x rows of the tile kPfDist tiles ahead (its diagonal block) are pulled into L2 while the
+    // current tiles are reduced: the gather then pays L2, not HBM, latency on first touch.  All
+    // CTAs advance at the same rate, so the off-diagonal neighbours (owned by other CTAs' ranges)
+    // are covered by their owners' prefetches.
+    constexpr int kPfDist = 4;
+    const bool pf_ok = ((reinterpret_cast<uintptr_t>(x) | (uintptr_t)(ldx * 8)) & 15) == 0;
+    auto prefetch_x = [&](int64_t t) {
+      if (!pf_ok || t >= t_end) return;
+      const int64_t r0 = t * R;
+      const uint32_t bytes = (uint32_t)(min((int64_t)R, n_rows - r0) * 8) & ~15u;
+      if (bytes == 0) return;
+#pragma unroll
+      for (int k = 0; k < K; ++k) bulk_prefetch_l2(x + (size_t)k * ldx + r0, bytes);
+    };
+    if (lane == 0)
+      for (int d = 0; d < kPfDist; ++d) prefetch_x(t_begin + d);
+    for (int64_t tb = t_begin; tb < t_end; tb += 32) {
+      const int64_t t = tb + lane;
+      int32_t sb = 0, se = 0;
+      if (t < t_end) {
+        sb = __ldg(rowptr + t * R);
+        se = __ldg(rowptr + min((t + 1) * (int64_t)R, n_rows));
       }
-      __syncthreads();
-      const int32_t lo = max(my_b, base), hi = min(my_e, base + cnt);
-      for (int32_t e = lo; e < hi; ++e) {
-        const double v = sv[e - base];
-        const int32_t c = sc[e - base];
-        if (c < n_owned) {
-#pragma unroll
-          for (int k = 0; k < K; ++k) acc[k] = fma(v, __ldg(x + (size_t)k * ldx + c), acc[k]);
-        } else {
-          has_ghost = true;
-          if (!skip_ghost_rows) {
-#pragma unroll
-            for (int k = 0; k < K; ++k)
-              acc[k] = fma(v, __ldg(xg + (size_t)k * ldg + (c - n_owned)), acc[k]);
-          }
+      const int nt = (int)min((int64_t)32, t_end - tb);
+      for (int i = 0; i < nt; ++i) {
+        const int32_t b = __shfl_sync(0xffffffffu, sb, i), e = __shfl_sync(0xffffffffu, se, i);
+        if (lane == 0) {
+          const int64_t r0 = (tb + i) * R;
+          prefetch_x(tb + i + kPfDist);
+          const uint32_t rp_cnt = (uint32_t)min((int64_t)kRp, (n_rows + 1 - r0 + 3) & ~(int64_t)3);
+          int32_t base = b;
+          do {
+            const int32_t cnt = min(g.cap, e - base);
+            // 128-B aligned sources and sizes: the bulk-copy engine moves unaligned requests in
+            // 16-B pieces (measured: 8 B/clk/SM instead of the full rate)
+            const int32_t g0 = base & ~31;
+            const uint32_t c4 = (uint32_t)(base + cnt - g0 + 31) & ~31u;
+            mbar_wait(&empty_bar[s], ph ^ 1u);
+            unsigned char* st = stage0 + (size_t)s * g.stage_bytes;
+            mbar_expect_tx(&full_bar[s], c4 * 12u + rp_cnt * 4u);
+            if (c4) {
+              bulk_load_1d(st, values + g0, c4 * 8u, &full_bar[s], pol);
+              bulk_load_1d(st + off_c, colind + g0, c4 * 4u, &full_bar[s], pol);
+            }
+            bulk_load_1d(st + off_rp, rowptr + r0, rp_cnt * 4u, &full_bar[s], pol);
+            if (++s == g.nstage) { s = 0; ph ^= 1u; }
+            base += g.cap;
+          } while (base < e);
         }
       }
     }
-    if (r < n_rows && !(skip_ghost_rows && has_ghost)) {
+    __syncwarp();
+  } else {
+    // ---------------------------------------------------------------- consumer warps
+    const int row_t = threadIdx.x % R;          // row of the tile
+    const int kgrp = threadIdx.x / R;           // right-hand-side group (warp-uniform)
+    const double* xcol[KT];                     // column bases: one IMAD.WIDE per gather
+    const double* gcol[KT];
 #pragma unroll
-      for (int k = 0; k < K; ++k) {
-        y[(size_t)k * ldy + r] = acc[k];
-        if (FUSE) ss[k] = fma(acc[k], acc[k], ss[k]);
+    for (int k = 0; k < KT; ++k) {
+      xcol[k] = x + (size_t)(kgrp * KT + k) * ldx;
+      gcol[k] = (MODE == SPMM_GHOST) ? xg + (size_t)(kgrp * KT + k) * ldg - n_owned : nullptr;
+    }
+    double* yk = y + (size_t)(kgrp * KT) * ldy;
+    int s = 0;
+    uint32_t ph = 0;
+    for (int64_t tile = t_begin; tile < t_end; ++tile) {
+      const int64_t r0 = tile * R;
+      const int64_t r = r0 + row_t;
+      const int nr = (int)min((int64_t)R, n_rows - r0);
+      double acc[KT];
+#pragma unroll
+      for (int k = 0; k < KT; ++k) acc[k] = 0.0;
+      bool has_ghost = false;
+      int32_t my_b = 0, my_e = 0, base = 0, seg_e = 0;
+      bool first = true;
+      do {
+        mbar_wait(&full_bar[s], ph);
+        const unsigned char* st = stage0 + (size_t)s * g.stage_bytes;
+        if (first) {
+          const int32_t* srp = reinterpret_cast<const int32_t*>(st + off_rp);
+          base = srp[0];
+          seg_e = srp[nr];
+          if (row_t < nr) {
+            my_b = srp[row_t];
+            my_e = srp[row_t + 1];
+          }
+          first = false;
+        }
+        const int32_t cnt = min(g.cap, seg_e - base);
+        const int32_t g0 = base & ~31;
+        const int32_t lo = max(my_b, base), hi = min(my_e, base + cnt);
+        const double* pv = reinterpret_cast<const double*>(st) + (lo - g0);
+        const int32_t* pc = reinterpret_cast<const int32_t*>(st + off_c) + (lo - g0);
+        for (int32_t e = lo; e < hi; e += U, pv += U, pc += U) {
+          // entries past the row end (within the stage's slack) are read but never used: their
+          // column index is replaced by 0 and their FMAs are predicated off
+          double v[U];
+          int32_t c[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            v[u] = pv[u];
+            c[u] = (e + u < hi) ? pc[u] : 0;
+          }
+          double xv[U][KT];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            if (MODE == SPMM_GHOST) {
+              const bool gh = c[u] >= n_owned;
+              has_ghost |= gh;
+#pragma unroll
+              for (int k = 0; k < KT; ++k) xv[u][k] = ld_gather((gh ? gcol[k] : xcol[k]) + c[u]);
+            } else {
+#pragma unroll
+              for (int k = 0; k < KT; ++k) xv[u][k] = ld_gather(xcol[k] + c[u]);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int k = 0; k < KT; ++k) pin(xv[u][k]);
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+            if (e + u < hi) {
+#pragma unroll
+              for (int k = 0; k < KT; ++k) acc[k] = fma(v[u], xv[u][k], acc[k]);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[s]);
+        if (++s == g.nstage) { s = 0; ph ^= 1u; }
+        base += g.cap;
+      } while (base < seg_e);
+      if (row_t < nr && !(MODE == SPMM_GHOST && skip_ghost_rows && has_ghost)) {
+#pragma unroll
+        for (int k = 0; k < KT; ++k) {
+          yk[(size_t)k * ldy + r] = acc[k];
+          if (MODE == SPMM_FUSE) ss[k] = fma(acc[k], acc[k], ss[k]);
+        }
       }
     }
   }
-  if (!FUSE) return;
-  __syncthreads();  // sv is reused as reduction scratch
-  double(*red)[K] = reinterpret_cast<double(*)[K]>(sv);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (MODE != SPMM_FUSE) return;
+  if (warp < kNWC) {
 #pragma unroll
-  for (int k = 0; k < K; ++k) {
-    const double t = warp_sum(ss[k]);
-    if (lane == 0) red[warp][k] = t;
+    for (int k = 0; k < KT; ++k) {
+      const double t = warp_sum(ss[k]);
+      if (lane == 0) red[warp][k] = t;
+    }
   }
   __syncthreads();
   if (threadIdx.x < K) {
+    // right-hand side k belongs to group k / KT, i.e. to the warps [grp * R / 32, (grp + 1) * R / 32)
+    const int grp = threadIdx.x / KT, kk = threadIdx.x % KT;
     double t = 0.0;
 #pragma unroll
-    for (int w = 0; w < kRows / 32; ++w) t += red[w][threadIdx.x];
+    for (int w = 0; w < R / 32; ++w) t += red[grp * (R / 32) + w][kk];
     fd.ws[(size_t)threadIdx.x * gridDim.x + blockIdx.x] = t;
   }
-  if (!fold_partials_wide<kRows / 32>(fd.ws, fd.ticket, K, gridDim.x, blockIdx.x, 1, fd.out)) return;
+  if (!fold_partials_wide<kNWC + 1>(fd.ws, fd.ticket, K, gridDim.x, blockIdx.x, 1, fd.out)) return;
   publish_flag(fd.flag, fd.seq);
 }
 
@@ -148,35 +300,90 @@ __global__ void __launch_bounds__(256)
     buf[(size_t)j * cnt + i] = __ldg(x + (size_t)j * ldx + idx[i]);
 }
 
-template <int K>
-int spmm_t(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, const double* x,
-           int64_t ldx, const double* xg, int64_t ldg, double* y, int64_t ldy, int skip,
-           const FusedDots& fd) {
-  if (rows == nullptr) {
-    const int64_t ntiles = (op->n_local + kRows - 1) / kRows;
-    if (ntiles == 0) return 0;
-    static int per_sm = 0;  // resident CTAs per SM of this instantiation
-    if (per_sm == 0) {
-      B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spmm_stream_kernel<K, true>,
-                                                              kRows, 0));
-      per_sm = std::max(per_sm, 1);
-    }
-    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)ctx->num_sms * per_sm);
-    if (fd.out)
-      spmm_stream_kernel<K, true><<<grid, kRows, 0, ctx->stream>>>(
-          op->rowptr, op->colind, op->values, op->n_local, (int32_t)op->n_local, x, ldx, xg, ldg,
-          y, ldy, skip, fd);
-    else
-      spmm_stream_kernel<K, false><<<grid, kRows, 0, ctx->stream>>>(
-          op->rowptr, op->colind, op->values, op->n_local, (int32_t)op->n_local, x, ldx, xg, ldg,
-          y, ldy, skip, fd);
-  } else {
-    if (nrows == 0) return 0;
-    const unsigned grid = (unsigned)((nrows + 255) / 256);
-    spmm_rows_kernel<K><<<grid, 256, 0, ctx->stream>>>(rows, nrows, op->rowptr, op->colind,
-                                                        op->values, (int32_t)op->n_local, x, ldx,
-                                                        xg, ldg, y, ldy);
+// stage geometry for R-row tiles of this operator: one chunk per tile whenever two stages of the
+// largest tile fit the shared-memory budget; as many resident CTAs (<= 3) and stages as fit
+SpmmGeom spmm_geom(const Op* op, int R, int* ctas_per_sm) {
+  const int64_t mt = op->max_tile_nnz[R == 64 ? 0 : R == 128 ? 1 : 2];
+  SpmmGeom g;
+  g.cap = (int)std::min<int64_t>(kCapMax, std::max<int64_t>((mt + 63) / 64 * 64, 64));
+  g.stage_bytes = ((g.cap + kSlack) * 12 + (R + 4) * 4 + 127) / 128 * 128;
+  static const int force_stages = [] {
+    const char* e = getenv("B200_SPMM_STAGES");
+    return e ? atoi(e) : 0;
+  }();
+  static const int force_ctas = [] {
+    const char* e = getenv("B200_SPMM_CTAS");
+    return e ? atoi(e) : 0;
+  }();
+  int ctas = 3;
+  while (ctas > 1 && (size_t)ctas * (2 * g.stage_bytes + 1280) > kSpmmSmemBudget) --ctas;
+  if (force_ctas > 0) ctas = std::min(ctas, force_ctas);
+  int nst = (int)((kSpmmSmemBudget / ctas - 1280) / g.stage_bytes);
+  nst = std::max(2, std::min(nst, kMaxStagesSpmm));
+  if (force_stages >= 2) nst = std::min(nst, force_stages);
+  g.nstage = nst;
+  *ctas_per_sm = ctas;
+  return g;
+}
+
+template <int K, int T, int MODE>
+int spmm_stream(Ctx* ctx, const Op* op, const double* x, int64_t ldx, const double* xg,
+                int64_t ldg, double* y, int64_t ldy, int skip, const FusedDots& fd) {
+  constexpr int R = kThreadsC / T;
+  const int64_t ntiles = (op->n_local + R - 1) / R;
+  if (ntiles == 0) return 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(spmm_stream_kernel<K, T, MODE>,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)kSpmmSmemBudget + 128));
+    attr_set = true;
   }
+  int ctas = 1;
+  const SpmmGeom g = spmm_geom(op, R, &ctas);
+  const int smem = g.nstage * g.stage_bytes + 128;
+  const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)ctx->num_sms * ctas);
+  spmm_stream_kernel<K, T, MODE><<<grid, kThreadsC + 32, smem, ctx->stream>>>(
+      op->rowptr, op->colind, op->values, op->n_local, (int32_t)op->n_local, x, ldx, xg, ldg, y,
+      ldy, skip, g, fd);
+  ++ctx->launches;
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int K, int T>
+int spmm_mode(Ctx* ctx, const Op* op, const double* x, int64_t ldx, const double* xg, int64_t ldg,
+              double* y, int64_t ldy, int skip, const FusedDots& fd) {
+  if (op->n_ghost > 0)
+    return spmm_stream<K, T, SPMM_GHOST>(ctx, op, x, ldx, xg, ldg, y, ldy, skip, fd);
+  if (fd.out) return spmm_stream<K, T, SPMM_FUSE>(ctx, op, x, ldx, xg, ldg, y, ldy, skip, fd);
+  return spmm_stream<K, T, SPMM_PLAIN>(ctx, op, x, ldx, xg, ldg, y, ldy, skip, fd);
+}
+
+// threads per row-tile split: long rows (27-point stencils) keep all 256 consumer threads busy on
+// a tile that still fits one stage by giving each of T thread groups K/T right-hand sides
+int spmm_split(const Op* op, int K) {
+  static const int force = [] {
+    const char* e = getenv("B200_SPMM_SPLIT");
+    return e ? atoi(e) : 0;
+  }();
+  int T = 1;
+  const double avg = op->n_local > 0 ? (double)op->nnz / (double)op->n_local : 0.0;
+  if (avg > 8.0 && K >= 2) T = 2;
+  if (force > 0) T = force;
+  while (T > 1 && (K % T != 0 || T > 4)) T >>= 1;
+  if (K >= 16 && T < 2) T = 4;  // at most 8 right-hand sides per thread (register budget)
+  return T;
+}
+
+template <int K>
+int spmm_rows(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, const double* x,
+              int64_t ldx, const double* xg, int64_t ldg, double* y, int64_t ldy) {
+  if (nrows == 0) return 0;
+  const unsigned grid = (unsigned)((nrows + 255) / 256);
+  spmm_rows_kernel<K><<<grid, 256, 0, ctx->stream>>>(rows, nrows, op->rowptr, op->colind,
+                                                      op->values, (int32_t)op->n_local, x, ldx, xg,
+                                                      ldg, y, ldy);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
   return 0;
@@ -195,22 +402,38 @@ int launch_spmm(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, cons
   while (k0 < k) {
     const int rem = k - k0;
     int step;
-    if (rem >= 8) step = 8; else if (rem >= 4) step = 4; else if (rem >= 2) step = 2; else step = 1;
+    if (rem >= 16) step = 16; else if (rem >= 8) step = 8; else if (rem >= 4) step = 4; else if (rem >= 2) step = 2; else step = 1;
     const double* xk = x + (size_t)k0 * ldx;
     const double* xgk = xg ? xg + (size_t)k0 * ldg : nullptr;
     double* yk = y + (size_t)k0 * ldy;
-    int rc;
+    int rc = 0;
     FusedDots fd;
-    if (fused && fused->out && rows == nullptr && !skip) {
+    if (fused && fused->out && rows == nullptr && !skip && op->n_ghost == 0) {
       fd = *fused;
       fd.out = fused->out + k0;
       if (k0 + step < k) fd.flag = nullptr;
     }
-    switch (step) {
-      case 8: rc = spmm_t<8>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip, fd); break;
-      case 4: rc = spmm_t<4>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip, fd); break;
-      case 2: rc = spmm_t<2>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip, fd); break;
-      default: rc = spmm_t<1>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy, skip, fd); break;
+    if (rows != nullptr) {
+      switch (step) {
+        case 16: rc = spmm_rows<16>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy); break;
+        case 8: rc = spmm_rows<8>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy); break;
+        case 4: rc = spmm_rows<4>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy); break;
+        case 2: rc = spmm_rows<2>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy); break;
+        default: rc = spmm_rows<1>(ctx, op, rows, nrows, xk, ldx, xgk, ldg, yk, ldy); break;
+      }
+    } else {
+      const int T = spmm_split(op, step);
+#define B200_SPMM_CASE(KK, TT) \
+  case KK * 8 + TT: rc = spmm_mode<KK, TT>(ctx, op, xk, ldx, xgk, ldg, yk, ldy, skip, fd); break;
+      switch (step * 8 + T) {
+        B200_SPMM_CASE(16, 4) B200_SPMM_CASE(16, 2)
+        B200_SPMM_CASE(8, 4) B200_SPMM_CASE(8, 2) B200_SPMM_CASE(8, 1)
+        B200_SPMM_CASE(4, 4) B200_SPMM_CASE(4, 2) B200_SPMM_CASE(4, 1)
+        B200_SPMM_CASE(2, 2) B200_SPMM_CASE(2, 1)
+        B200_SPMM_CASE(1, 1)
+        default: return B200_ERR_ARG;
+      }
+#undef B200_SPMM_CASE
     }
     if (rc) return rc;
     k0 += step;
