@@ -62,24 +62,36 @@ bool columns_overlap(const MV* a, const MV* b) {
   return false;
 }
 
-// A mailbox slot + sequence number for a kernel with a fused reduction epilogue (single rank
-// only: multi-rank results would still need their allreduce).  Remembered products that were
-// still waiting in the recycled slot are dropped.
+// A mailbox slot + sequence number for a kernel with a fused reduction epilogue.  Single rank: the
+// kernel's last CTA publishes straight into the mailbox.  Multi-rank (peer windows available): the
+// kernel leaves this rank's partial sums in a device slot and fused_finish() queues the one-CTA
+// exchange kernel that folds all ranks' partials into the mailbox -- still without a host round
+// trip.  Remembered products that were still waiting in the recycled slot are dropped.
 bool fused_slot(Ctx* ctx, FusedDots* fd, size_t* src) {
-  if (!ctx->fuse || ctx->nranks != 1) return false;
+  if (!ctx->fuse || (ctx->nranks != 1 && !ctx->p2p)) return false;
   const int slot = ctx->aux_next;
   ctx->aux_next = (slot + 1) % kAuxSlots;
   const size_t base = kAuxBase + (size_t)slot * kAuxSlotDoubles;
   for (int i = 0; i < kDotCache; ++i)
     if (ctx->dots[i].seq != 0 && ctx->dots[i].src >= base && ctx->dots[i].src < base + kAuxSlotDoubles)
       ctx->dots[i] = Ctx::DotEntry();
-  fd->out = ctx->mbox_d + base;
-  fd->flag = ctx->flag_d;
+  if (ctx->nranks == 1) {
+    fd->out = ctx->mbox_d + base;
+    fd->flag = ctx->flag_d;
+  } else {
+    fd->out = ctx->aux_d + (size_t)slot * kAuxSlotDoubles;
+    fd->flag = nullptr;
+  }
   fd->seq = ++ctx->seq;
   fd->ws = ctx->ws;
   fd->ticket = ctx->ticket;
   *src = base;
   return true;
+}
+
+int fused_finish(Ctx* ctx, const FusedDots& fd, size_t src, int count) {
+  if (ctx->nranks == 1) return 0;
+  return launch_xchg_publish(ctx, fd.out, ctx->mbox_d + src, count, false, fd.seq);
 }
 
 // Park-Miller jump: seed * 16807^e mod (2^31-1)
@@ -458,6 +470,7 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
     jv += lv;
   }
   mv->touch(0, q);
+  if (fuse) B200_TRY(fused_finish(ctx, fd, src, 2 * q));
   if (fuse)
     for (int j = 0; j < q; ++j) {
       const uint64_t nid = mv->id(j);
@@ -747,6 +760,7 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
       rc = launch_spmm(ctx, op, nullptr, 0, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr);
       ctx->t_end();
       y->touch(j, len);
+      if (fuse && !rc) rc = fused_finish(ctx, fd, src, k);
       if (fuse && !rc)
         for (int c = 0; c < k; ++c) ctx->remember_dot(y->id(c), y->id(c), 0.0, fd.seq, src + c);
     } else {

@@ -141,6 +141,65 @@ __global__ void publish_kernel(const double* __restrict__ src, double* __restric
 }
 }  // namespace
 
+namespace {
+// One CTA per rank.  (1) this rank's partial result -> slot [parity][me] of every rank's window
+// (own window included) over NVLink; (2) one release-store of the exchange number per peer flag;
+// (3) acquire-spin until every peer's flag for this exchange has arrived in the own window;
+// (4) fold the contributions in rank order -- the same order on every rank, so the replicated
+// host-side Belos state cannot diverge -- into the host mailbox and release the host flag.
+// A window half is re-used two exchanges later; a peer can only be that far ahead after it has seen
+// this rank's flag of the exchange in between, which this rank raises after it finished reading.
+template <bool IS_MAX>
+__global__ void __launch_bounds__(256)
+    xchg_publish_kernel(XchgWindow w, const double* __restrict__ src, double* __restrict__ dst,
+                        int count, uint64_t xseq, uint64_t* flag, uint64_t seq) {
+  const int par = (int)(xseq & 1u);
+  const int P = w.nranks, me = w.rank;
+  for (int r = 0; r < P; ++r) {
+    double* slot = reinterpret_cast<double*>(static_cast<char*>(w.win[r]) + kXchgFlagBytes) +
+                   ((size_t)par * kMaxPeers + me) * kXchgMax;
+    for (int i = threadIdx.x; i < count; i += blockDim.x) slot[i] = src[i];
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < P) {
+    uint64_t* pf = reinterpret_cast<uint64_t*>(static_cast<char*>(w.win[threadIdx.x]) + par * 256) + me;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pf), "l"(xseq) : "memory");
+    const uint64_t* mf = reinterpret_cast<const uint64_t*>(static_cast<char*>(w.win[me]) + par * 256) +
+                         threadIdx.x;
+    uint64_t v;
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mf) : "memory");
+    } while (v < xseq);
+  }
+  __syncthreads();
+  const double* mine = reinterpret_cast<const double*>(static_cast<char*>(w.win[me]) + kXchgFlagBytes) +
+                       (size_t)par * kMaxPeers * kXchgMax;
+  for (int i = threadIdx.x; i < count; i += blockDim.x) {
+    double t = __ldcg(mine + i);
+    for (int r = 1; r < P; ++r) {
+      const double v = __ldcg(mine + (size_t)r * kXchgMax + i);
+      t = IS_MAX ? fmax(t, v) : t + v;
+    }
+    dst[i] = t;
+  }
+  publish_flag(flag, seq);
+}
+}  // namespace
+
+int launch_xchg_publish(Ctx* ctx, const double* src_d, double* dst, int count, bool is_max,
+                        uint64_t seq) {
+  ++ctx->xseq;
+  if (is_max)
+    xchg_publish_kernel<true><<<1, 256, 0, ctx->stream>>>(ctx->xw, src_d, dst, count, ctx->xseq,
+                                                         ctx->flag_d, seq);
+  else
+    xchg_publish_kernel<false><<<1, 256, 0, ctx->stream>>>(ctx->xw, src_d, dst, count, ctx->xseq,
+                                                          ctx->flag_d, seq);
+  ++ctx->launches;
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int launch_publish(Ctx* ctx, int count) {
   publish_kernel<<<1, 256, 0, ctx->stream>>>(ctx->red_d, ctx->mbox_d, count, ctx->flag_d,
                                              ctx->seq);

@@ -250,9 +250,13 @@ bool Ctx::recall_dot(uint64_t a, uint64_t b, double* val, int* rc) {
 
 int Ctx::finish_reduction(int count, bool is_max) {
   if (nranks > 1) {
-    B200_TRY(nccl_allreduce_f64(this, red_d, (size_t)count, is_max, stream));
-    ++launches;
-    B200_TRY(launch_publish(this, count));
+    if (p2p && count <= kXchgMax) {
+      B200_TRY(launch_xchg_publish(this, red_d, mbox_d, count, is_max, seq));
+    } else {
+      B200_TRY(nccl_allreduce_f64(this, red_d, (size_t)count, is_max, stream));
+      ++launches;
+      B200_TRY(launch_publish(this, count));
+    }
   }
   return wait_flag(seq);
 }
@@ -296,6 +300,7 @@ extern "C" int b200_ctx_create(int device, b200_ctx** out) {
   B200_CUDA(cudaMalloc((void**)&c->ticket, kTicketBytes));
   B200_CUDA(cudaMemset(c->ticket, 0, kTicketBytes));
   B200_CUDA(cudaMalloc((void**)&c->red_d, kMailboxDoubles * sizeof(double)));
+  B200_CUDA(cudaMalloc((void**)&c->aux_d, (size_t)kAuxSlots * kAuxSlotDoubles * sizeof(double)));
   B200_CUDA(cudaMalloc((void**)&c->dB, kStageSlotBytes));
   B200_CUDA(cudaHostAlloc((void**)&c->stage_h, kStageSlots * kStageSlotBytes, cudaHostAllocDefault));
   for (int i = 0; i < kStageSlots; ++i)
@@ -309,6 +314,9 @@ extern "C" int b200_ctx_destroy(b200_ctx* c) {
   if (!c) return 0;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
+  for (int r = 0; r < c->xw.nranks; ++r)
+    if (r != c->xw.rank && c->xw.win[r]) cudaIpcCloseMemHandle(c->xw.win[r]);
+  if (c->xwin) cudaFree(c->xwin);
   if (c->comm && c->nccl) c->nccl->CommDestroy(c->comm);
   for (auto& kv : c->pool) cudaFree(kv.second);
   c->pool.clear();
@@ -320,6 +328,7 @@ extern "C" int b200_ctx_destroy(b200_ctx* c) {
   cudaFree(c->ws);
   cudaFree(c->ticket);
   cudaFree(c->red_d);
+  cudaFree(c->aux_d);
   cudaFree(c->dB);
   if (c->flush_buf) cudaFree(c->flush_buf);
   cudaEventDestroy(c->ev_comm);
@@ -334,6 +343,58 @@ extern "C" int b200_ctx_sync(b200_ctx* c) {
   if (!c) return fail(B200_ERR_ARG, "null context");
   B200_CUDA(cudaStreamSynchronize(c->stream));
   B200_CUDA(cudaStreamSynchronize(c->comm_stream));
+  return 0;
+}
+
+// Map every rank's exchange window into this process (CUDA IPC; the 64-byte handles travel through
+// one int64 allreduce on the fresh communicator).  Any failure on any rank leaves all ranks on
+// the NCCL allreduce path (the decision is itself allreduced, so it is unanimous).
+static int setup_peer_windows(b200_ctx* c) {
+  const int P = c->nranks, me = c->rank;
+  const char* off = getenv("B200_NO_P2P");
+  int ok = (P <= kMaxPeers && !(off && off[0] == '1')) ? 1 : 0;
+  cudaIpcMemHandle_t mine;
+  std::memset(&mine, 0, sizeof(mine));
+  if (ok && cudaMalloc(&c->xwin, kXchgBytes) != cudaSuccess) ok = 0;
+  if (ok && cudaMemset(c->xwin, 0, kXchgBytes) != cudaSuccess) ok = 0;
+  if (ok && cudaIpcGetMemHandle(&mine, c->xwin) != cudaSuccess) ok = 0;
+  cudaGetLastError();
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  const size_t per = 9;  // 8 words of handle + 1 "ok" word per rank
+  std::vector<int64_t> h((size_t)P * per, 0);
+  std::memcpy(&h[(size_t)me * per], &mine, 64);
+  h[(size_t)me * per + 8] = ok;
+  int64_t* d = nullptr;
+  B200_CUDA(cudaMalloc((void**)&d, h.size() * sizeof(int64_t)));
+  B200_CUDA(cudaMemcpy(d, h.data(), h.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+  B200_TRY(nccl_allreduce_i64(c, d, h.size(), c->stream));
+  B200_CUDA(cudaMemcpyAsync(h.data(), d, h.size() * sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+  B200_CUDA(cudaStreamSynchronize(c->stream));
+  for (int r = 0; r < P; ++r) ok = ok && h[(size_t)r * per + 8] == 1;
+  c->xw.nranks = P;
+  c->xw.rank = me;
+  for (int r = 0; r < P && ok; ++r) {
+    if (r == me) {
+      c->xw.win[r] = c->xwin;
+      continue;
+    }
+    cudaIpcMemHandle_t hr;
+    std::memcpy(&hr, &h[(size_t)r * per], 64);
+    if (cudaIpcOpenMemHandle(&c->xw.win[r], hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      cudaGetLastError();
+      ok = 0;
+    }
+  }
+  // unanimous decision (an open can fail on one rank only)
+  int64_t v = ok;
+  B200_CUDA(cudaMemcpy(d, &v, sizeof(v), cudaMemcpyHostToDevice));
+  B200_TRY(nccl_allreduce_i64(c, d, 1, c->stream));
+  B200_CUDA(cudaMemcpyAsync(&v, d, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
+  B200_CUDA(cudaStreamSynchronize(c->stream));
+  cudaFree(d);
+  c->p2p = (v == P);
+  if (getenv("B200_VERBOSE"))
+    fprintf(stderr, "[b200 rank %d/%d] peer windows: %s\n", me, P, c->p2p ? "on" : "off (NCCL allreduce)");
   return 0;
 }
 
@@ -363,7 +424,7 @@ extern "C" int b200_ctx_comm_init(b200_ctx* c, const void* id128, int nranks, in
   c->comm = comm;
   c->rank = rank;
   c->nranks = nranks;
-  return 0;
+  return setup_peer_windows(c);
 }
 
 extern "C" int b200_ctx_rank(const b200_ctx* c, int* rank, int* nranks) {

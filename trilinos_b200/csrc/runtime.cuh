@@ -47,6 +47,17 @@ constexpr size_t kStageSlotBytes = 512u << 10; // host B blocks for MvTimesMatAd
 
 struct NcclApi;  // dlopen'ed function table (runtime.cu)
 
+// peer-memory exchange windows (see Ctx::xw).  Window layout: flags[2][kMaxPeers] (uint64, one
+// 256-B block per parity) followed by data[2][kMaxPeers][kXchgMax] doubles.
+constexpr int kMaxPeers = 8;
+constexpr int kXchgMax = 4096;   // largest result (doubles) exchanged through the windows
+constexpr size_t kXchgFlagBytes = 2 * 256;
+constexpr size_t kXchgBytes = kXchgFlagBytes + (size_t)2 * kMaxPeers * kXchgMax * sizeof(double);
+struct XchgWindow {
+  void* win[kMaxPeers] = {};     // win[r]: rank r's window as mapped in this process
+  int nranks = 1, rank = 0;
+};
+
 // where a kernel with a fused reduction epilogue puts its column dot products
 struct FusedDots {
   double* out = nullptr;        // device-visible mailbox slot (nullptr: no epilogue)
@@ -77,12 +88,22 @@ struct Ctx {
   double* ws = nullptr;            // per-CTA partials
   unsigned int* ticket = nullptr;  // last-block election counter (self-resetting)
   double* red_d = nullptr;         // device-side result (multi-rank: allreduce in place)
+  double* aux_d = nullptr;         // multi-rank: per-rank partials of fused epilogues (kAuxSlots slots)
   double* dB = nullptr;            // device copy of the host dense block B
   char* stage_h = nullptr;         // pinned staging ring for B
   cudaEvent_t stage_ev[kStageSlots] = {};
   bool stage_used[kStageSlots] = {};
   int stage_next = 0;
   void* flush_buf = nullptr;       // > L2 scratch for bench hygiene
+  // Peer-memory exchange for the small allreduces (multi-rank, one node): every rank's window is
+  // mapped into every other rank through CUDA IPC; a one-CTA kernel stores this rank's partial
+  // result into all windows over NVLink, raises a flag per peer, waits for the peers' flags and
+  // folds the contributions in rank order (bitwise identical on every rank) straight into the
+  // host mailbox.  Replaces ncclAllReduce + publish kernel (~30 us) by one ~6 us kernel.
+  XchgWindow xw;
+  void* xwin = nullptr;            // this rank's window (cudaMalloc, IPC-exported)
+  uint64_t xseq = 0;               // exchange counter (parity selects the window half)
+  bool p2p = false;
   // NCCL
   NcclApi* nccl = nullptr;
   void* comm = nullptr;
@@ -244,6 +265,9 @@ int launch_pack(Ctx*, cudaStream_t s, const int32_t* idx, int64_t cnt, const dou
 
 // the mailbox publish kernel used after a multi-rank allreduce
 int launch_publish(Ctx*, int count);
+// multi-rank with peer windows: exchange + fold + publish in one kernel (count <= kXchgMax)
+int launch_xchg_publish(Ctx*, const double* src_d, double* dst, int count, bool is_max,
+                        uint64_t seq);
 
 }  // namespace b200
 
