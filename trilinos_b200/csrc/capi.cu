@@ -542,6 +542,77 @@ int upload(T** dst, const std::vector<T>& src) {
 
 }  // namespace
 
+namespace {
+
+void halo_window_release(b200_op* op) {
+  for (size_t i = 0; i < op->peers.size() && i < (size_t)kMaxPeers; ++i)
+    if (op->peer_hwin[i]) {
+      cudaIpcCloseMemHandle(op->peer_hwin[i]);
+      op->peer_hwin[i] = nullptr;
+    }
+  if (op->hwin) cudaFree(op->hwin);
+  op->hwin = nullptr;
+  if (op->p2p_halo) op->recv_buf = nullptr;  // it pointed into the window
+  op->p2p_halo = false;
+}
+
+// (Re)allocate this rank's halo window for k right-hand sides and map the neighbours' windows.
+// Collective: every rank reaches it in the same Apply (the block width is the same everywhere).
+// Any failure on any rank, or a neighbour relation that is not mutual (a rank that only sends has
+// no back-pressure on the parity scheme), leaves all ranks on the NCCL send/recv path.
+int halo_window_setup(Ctx* ctx, b200_op* op, size_t k) {
+  const int P = ctx->nranks, me = ctx->rank;
+  B200_CUDA(cudaStreamSynchronize(ctx->stream));
+  B200_CUDA(cudaStreamSynchronize(ctx->comm_stream));
+  halo_window_release(op);
+  int ok = ctx->p2p && op->peers.size() <= (size_t)kMaxPeers ? 1 : 0;
+  for (const HaloPeer& pr : op->peers)
+    if (pr.send_cnt <= 0 || pr.recv_cnt <= 0) ok = 0;
+  const size_t half = ((size_t)op->n_ghost * k * sizeof(double) + 255) / 256 * 256;
+  const size_t bytes = 256 + 2 * half;
+  cudaIpcMemHandle_t mine;
+  std::memset(&mine, 0, sizeof(mine));
+  if (ok && cudaMalloc(&op->hwin, bytes) != cudaSuccess) ok = 0;
+  if (ok && cudaMemset(op->hwin, 0, bytes) != cudaSuccess) ok = 0;
+  if (ok && cudaIpcGetMemHandle(&mine, op->hwin) != cudaSuccess) ok = 0;
+  cudaGetLastError();
+  const size_t per = 9;
+  std::vector<int64_t> h((size_t)P * per, 0);
+  std::memcpy(&h[(size_t)me * per], &mine, 64);
+  h[(size_t)me * per + 8] = ok;
+  int64_t* d = nullptr;
+  B200_CUDA(cudaMalloc((void**)&d, h.size() * sizeof(int64_t)));
+  B200_CUDA(cudaMemcpy(d, h.data(), h.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+  B200_TRY(nccl_allreduce_i64(ctx, d, h.size(), ctx->stream));
+  B200_CUDA(cudaMemcpyAsync(h.data(), d, h.size() * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(cudaStreamSynchronize(ctx->stream));
+  for (int r = 0; r < P; ++r) ok = ok && h[(size_t)r * per + 8] == 1;
+  for (size_t i = 0; i < op->peers.size() && ok; ++i) {
+    cudaIpcMemHandle_t hr;
+    std::memcpy(&hr, &h[(size_t)op->peers[i].rank * per], 64);
+    if (cudaIpcOpenMemHandle(&op->peer_hwin[i], hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      cudaGetLastError();
+      op->peer_hwin[i] = nullptr;
+      ok = 0;
+    }
+  }
+  int64_t v = ok;
+  B200_CUDA(cudaMemcpy(d, &v, sizeof(v), cudaMemcpyHostToDevice));
+  B200_TRY(nccl_allreduce_i64(ctx, d, 1, ctx->stream));
+  B200_CUDA(cudaMemcpyAsync(&v, d, sizeof(v), cudaMemcpyDeviceToHost, ctx->stream));
+  B200_CUDA(cudaStreamSynchronize(ctx->stream));
+  cudaFree(d);
+  if (v != P) {
+    halo_window_release(op);
+    return 0;
+  }
+  op->p2p_halo = true;
+  op->hseq = 0;
+  return 0;
+}
+
+}  // namespace
+
 extern "C" int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_begin,
                                   int64_t row_end, const int32_t* rowptr,
                                   const int64_t* colind_global, const double* values,
@@ -694,8 +765,15 @@ extern "C" int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_b
       return rc;
     }
     for (int r = 0; r < P; ++r)
-      if (need[r] > 0 || send_cnt[r] > 0)
-        op->peers.push_back(HaloPeer{r, send_off[r], send_cnt[r], recv_off[r], need[r]});
+      if (need[r] > 0 || send_cnt[r] > 0) {
+        HaloPeer hp{r, send_off[r], send_cnt[r], recv_off[r], need[r]};
+        // rank r's ghosts are grouped by owner in ascending rank order (MakeColMap order)
+        for (int q2 = 0; q2 < P; ++q2) {
+          hp.remote_nghost += M[(size_t)r * P + q2];
+          if (q2 < me) hp.remote_off += M[(size_t)r * P + q2];
+        }
+        op->peers.push_back(hp);
+      }
   }
   *out = op;
   return 0;
@@ -710,6 +788,7 @@ extern "C" int b200_op_destroy(b200_op* op) {
   cudaFree(op->int_rows);
   cudaFree(op->send_idx);
   cudaFree(op->send_buf);
+  halo_window_release(op);  // (p2p: recv_buf pointed into the window and is reset here)
   cudaFree(op->recv_buf);
   cudaFree(op->xcol);
   delete op;
@@ -764,10 +843,56 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
       if (fuse && !rc)
         for (int c = 0; c < k; ++c) ctx->remember_dot(y->id(c), y->id(c), 0.0, fd.seq, src + c);
     } else {
-      // grow halo buffers
+      // grow halo buffers (collective: the block width is the same on every rank)
       if ((size_t)len > op->buf_k) {
-        cudaStreamSynchronize(ctx->stream);
-        cudaStreamSynchronize(ctx->comm_stream);
+        rc = halo_window_setup(ctx, op, (size_t)len);
+        if (rc) break;
+        if (op->p2p_halo) op->buf_k = (size_t)len;
+      }
+      if (op->p2p_halo) {
+        // peer-memory halo: put || interior rows -> boundary rows (which wait for the flags
+        // themselves); no NCCL call
+        const uint64_t hs = ++op->hseq;
+        const size_t half = ((size_t)op->n_ghost * op->buf_k * sizeof(double) + 255) / 256 * 256;
+        const size_t par = (size_t)(hs & 1u);
+        HaloPut hp;
+        HaloWait hw;
+        hp.npeers = hw.n = (int)op->peers.size();
+        hw.seq = hs;
+        for (int pi = 0; pi < hp.npeers; ++pi) {
+          const HaloPeer& pr = op->peers[pi];
+          const size_t rhalf = ((size_t)pr.remote_nghost * op->buf_k * sizeof(double) + 255) / 256 * 256;
+          char* rw = static_cast<char*>(op->peer_hwin[pi]);
+          hp.send_off[pi] = pr.send_off;
+          hp.send_cnt[pi] = pr.send_cnt;
+          hp.dst[pi] = reinterpret_cast<double*>(rw + 256 + par * rhalf) + pr.remote_off;
+          hp.dst_ld[pi] = pr.remote_nghost;
+          hp.flag[pi] = reinterpret_cast<uint64_t*>(rw) + ctx->rank;
+          hw.flag[pi] = reinterpret_cast<const uint64_t*>(op->hwin) + pr.rank;
+        }
+        op->recv_buf = reinterpret_cast<double*>(static_cast<char*>(op->hwin) + 256 + par * half);
+        // the put runs on the comm stream next to the interior rows; nothing on the compute
+        // stream waits for it except whatever follows this apply (x must stay intact until the
+        // put has read it)
+        if (cudaEventRecord(ctx->ev_compute, ctx->stream) != cudaSuccess ||
+            cudaStreamWaitEvent(ctx->comm_stream, ctx->ev_compute, 0) != cudaSuccess) {
+          rc = fail(B200_ERR_CUDA, "Apply: event handoff failed");
+          break;
+        }
+        rc = launch_halo_put(ctx, hp, op->send_idx, op->n_send, xp, x->ld, len, hs);
+        if (rc) break;
+        cudaEventRecord(ctx->ev_comm, ctx->comm_stream);
+        ctx->t_begin(K_SPMM, algo_bytes * len / k);
+        rc = launch_spmm(ctx, op, nullptr, -1, xp, x->ld, yp, y->ld, len);
+        if (!rc) rc = launch_spmm_boundary(ctx, op, hw, xp, x->ld, yp, y->ld, len);
+        ctx->t_end();
+        if (rc) break;
+        cudaStreamWaitEvent(ctx->stream, ctx->ev_comm, 0);
+        y->touch(j, len);
+        j += len;
+        continue;
+      }
+      if ((size_t)len > op->buf_k) {
         cudaFree(op->send_buf);
         cudaFree(op->recv_buf);
         op->send_buf = op->recv_buf = nullptr;

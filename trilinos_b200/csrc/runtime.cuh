@@ -206,6 +206,26 @@ struct HaloPeer {
   int rank;
   int64_t send_off, send_cnt;  // rows of mine the peer needs (offset into send_idx)
   int64_t recv_off, recv_cnt;  // ghost rows I get from the peer (offset into ghost tail)
+  int64_t remote_off = 0;      // where my rows start in the PEER's ghost tail
+  int64_t remote_nghost = 0;   // the peer's ghost count (leading dimension of its ghost block)
+};
+
+// Peer-memory halo ("put") arguments.  Every rank owns a halo window
+//   [256 B: one uint64 flag per source rank][ghost block, parity 0][ghost block, parity 1]
+// mapped into its neighbours through CUDA IPC.  The put kernel gathers the rows a neighbour needs
+// and stores them straight into that neighbour's ghost block over NVLink (final [rhs][ghost]
+// layout), then raises the neighbour's flag; the boundary-row kernel spins on its own flags.
+struct HaloPut {
+  int npeers = 0;
+  int64_t send_off[kMaxPeers], send_cnt[kMaxPeers];
+  double* dst[kMaxPeers];       // peer's ghost block (current parity) + remote_off
+  int64_t dst_ld[kMaxPeers];    // peer's n_ghost
+  uint64_t* flag[kMaxPeers];    // peer's flag word for this rank
+};
+struct HaloWait {
+  int n = 0;
+  const uint64_t* flag[kMaxPeers];
+  uint64_t seq = 0;
 };
 
 struct Op {
@@ -227,8 +247,13 @@ struct Op {
   double* xcol = nullptr;       // (n_local + n_ghost) x k column-map copy of x (multi-rank)
   int64_t xcol_ld = 0;
   int xcol_k = 0;
-  double* recv_buf = nullptr;
+  double* recv_buf = nullptr;   // ghost block the kernels read (p2p: the current parity's half)
   size_t buf_k = 0;
+  // peer-memory halo (see HaloPut)
+  bool p2p_halo = false;
+  void* hwin = nullptr;                 // own window
+  void* peer_hwin[kMaxPeers] = {};      // peers[i]'s window as mapped here
+  uint64_t hseq = 0;                    // applies done through the window (parity = hseq & 1)
   int max_row_nnz = 0;
   // largest nonzero count of any tile of 64 / 128 / 256 consecutive rows (SpMM stage sizing)
   int64_t max_tile_nnz[3] = {0, 0, 0};
@@ -262,6 +287,11 @@ int launch_spmm(Ctx*, const Op* op, const int32_t* rows, int64_t nrows, const do
                 int64_t ldx, double* y, int64_t ldy, int k, const FusedDots* fused = nullptr);
 int launch_pack(Ctx*, cudaStream_t s, const int32_t* idx, int64_t cnt, const double* x,
                 int64_t ldx, int k, double* buf);
+int launch_halo_put(Ctx*, const HaloPut& h, const int32_t* send_idx, int64_t n_send,
+                    const double* x, int64_t ldx, int k, uint64_t seq);
+// boundary rows after a peer-memory halo: the kernel waits for the neighbours' flags itself
+int launch_spmm_boundary(Ctx*, const Op* op, const HaloWait& w, const double* x, int64_t ldx,
+                         double* y, int64_t ldy, int k);
 
 // the mailbox publish kernel used after a multi-rank allreduce
 int launch_publish(Ctx*, int count);

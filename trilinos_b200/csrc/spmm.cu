@@ -210,8 +210,12 @@ __global__ void __launch_bounds__(kThreadsC + 32, 3)
             if (MODE == SPMM_GHOST) {
               const bool gh = c[u] >= n_owned;
               has_ghost |= gh;
+              // interior pass: the ghost block is being written by the neighbours right now and
+              // the row is dropped anyway -- read a harmless owned entry instead
+              const bool use_g = gh && !skip_ghost_rows;
+              const int32_t cc = (gh && skip_ghost_rows) ? 0 : c[u];
 #pragma unroll
-              for (int k = 0; k < KT; ++k) xv[u][k] = ld_gather((gh ? gcol[k] : xcol[k]) + c[u]);
+              for (int k = 0; k < KT; ++k) xv[u][k] = ld_gather((use_g ? gcol[k] : xcol[k]) + cc);
             } else {
 #pragma unroll
               for (int k = 0; k < KT; ++k) xv[u][k] = ld_gather(xcol[k] + c[u]);
@@ -269,8 +273,17 @@ __global__ void __launch_bounds__(256)
     spmm_rows_kernel(const int32_t* __restrict__ rows, int64_t nrows,
                      const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colind,
                      const double* __restrict__ values, int32_t n_owned,
-                     const double* __restrict__ x, int64_t ldx, const double* __restrict__ xg,
-                     int64_t ldg, double* __restrict__ y, int64_t ldy) {
+                     const double* __restrict__ x, int64_t ldx, const double* xg, int64_t ldg,
+                     double* __restrict__ y, int64_t ldy, HaloWait w) {
+  if (w.n > 0) {  // peer-memory halo: wait until every neighbour's put of this apply has landed
+    if ((int)threadIdx.x < w.n) {
+      uint64_t v;
+      do {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(w.flag[threadIdx.x]) : "memory");
+      } while (v < w.seq);
+    }
+    __syncthreads();
+  }
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nrows) return;
   const int32_t r = rows[i];
@@ -280,10 +293,14 @@ __global__ void __launch_bounds__(256)
   for (int32_t e = rowptr[r]; e < rowptr[r + 1]; ++e) {
     const double v = values[e];
     const int32_t c = colind[e];
-    const double* src = (c < n_owned) ? x + c : xg + (c - n_owned);
-    const int64_t ld = (c < n_owned) ? ldx : ldg;
+    // ghost entries were written by a peer GPU (possibly during this kernel): L2-coherent loads
+    if (c < n_owned) {
 #pragma unroll
-    for (int k = 0; k < K; ++k) acc[k] = fma(v, __ldg(src + (size_t)k * ld), acc[k]);
+      for (int k = 0; k < K; ++k) acc[k] = fma(v, __ldg(x + c + (size_t)k * ldx), acc[k]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < K; ++k) acc[k] = fma(v, __ldcg(xg + (c - n_owned) + (size_t)k * ldg), acc[k]);
+    }
   }
 #pragma unroll
   for (int k = 0; k < K; ++k) y[(size_t)k * ldy + r] = acc[k];
@@ -324,6 +341,35 @@ SpmmGeom spmm_geom(const Op* op, int R, int* ctas_per_sm) {
   g.nstage = nst;
   *ctas_per_sm = ctas;
   return g;
+}
+
+// peer-memory halo put: dst_p[j * ld_p + i] = x[send_idx[off_p + i] + j * ldx] for every neighbour p
+// (the neighbour's ghost block, over NVLink), then the last CTA raises the neighbours' flags
+__global__ void __launch_bounds__(256)
+    halo_put_kernel(HaloPut h, const int32_t* __restrict__ send_idx, const double* __restrict__ x,
+                    int64_t ldx, uint64_t seq, unsigned int* ticket) {
+  const int j = blockIdx.y;
+  for (int p = 0; p < h.npeers; ++p) {
+    const int32_t* idx = send_idx + h.send_off[p];
+    double* dst = h.dst[p] + (size_t)j * h.dst_ld[p];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < h.send_cnt[p];
+         i += (int64_t)gridDim.x * blockDim.x)
+      dst[i] = __ldg(x + (size_t)j * ldx + idx[i]);
+  }
+  __shared__ bool is_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();  // cumulative over the CTA's stores ordered by the barrier
+    const unsigned int total = gridDim.x * gridDim.y;
+    const unsigned int t = atomicAdd(ticket, 1u);
+    is_last = (t == total - 1);
+    if (is_last) *ticket = 0u;
+  }
+  __syncthreads();
+  if (is_last && (int)threadIdx.x < h.npeers) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(h.flag[threadIdx.x]), "l"(seq) : "memory");
+  }
 }
 
 template <int K, int T, int MODE>
@@ -378,12 +424,13 @@ int spmm_split(const Op* op, int K) {
 
 template <int K>
 int spmm_rows(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, const double* x,
-              int64_t ldx, const double* xg, int64_t ldg, double* y, int64_t ldy) {
+              int64_t ldx, const double* xg, int64_t ldg, double* y, int64_t ldy,
+              const HaloWait& w = HaloWait()) {
   if (nrows == 0) return 0;
   const unsigned grid = (unsigned)((nrows + 255) / 256);
   spmm_rows_kernel<K><<<grid, 256, 0, ctx->stream>>>(rows, nrows, op->rowptr, op->colind,
                                                       op->values, (int32_t)op->n_local, x, ldx, xg,
-                                                      ldg, y, ldy);
+                                                      ldg, y, ldy, w);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
   return 0;
@@ -434,6 +481,42 @@ int launch_spmm(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, cons
         default: return B200_ERR_ARG;
       }
 #undef B200_SPMM_CASE
+    }
+    if (rc) return rc;
+    k0 += step;
+  }
+  return 0;
+}
+
+int launch_halo_put(Ctx* ctx, const HaloPut& h, const int32_t* send_idx, int64_t n_send,
+                    const double* x, int64_t ldx, int k, uint64_t seq) {
+  if (k <= 0) return 0;
+  // few, fat CTAs: each pays one system-scope fence (remote-store acknowledgement) at its end
+  const unsigned bx = (unsigned)std::max<int64_t>(1, std::min<int64_t>((n_send + 2047) / 2048, 32));
+  halo_put_kernel<<<dim3(bx, (unsigned)k), 256, 0, ctx->comm_stream>>>(
+      h, send_idx, x, ldx, seq, ctx->ticket + kTicketBytes / sizeof(unsigned int) - 1);
+  ++ctx->launches;
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int launch_spmm_boundary(Ctx* ctx, const Op* op, const HaloWait& w, const double* x, int64_t ldx,
+                         double* y, int64_t ldy, int k) {
+  const double* xg = op->recv_buf;
+  const int64_t ldg = op->n_ghost;
+  for (int k0 = 0; k0 < k;) {
+    const int rem = k - k0;
+    const int step = rem >= 16 ? 16 : rem >= 8 ? 8 : rem >= 4 ? 4 : rem >= 2 ? 2 : 1;
+    const double* xk = x + (size_t)k0 * ldx;
+    const double* xgk = xg + (size_t)k0 * ldg;
+    double* yk = y + (size_t)k0 * ldy;
+    int rc;
+    switch (step) {
+      case 16: rc = spmm_rows<16>(ctx, op, op->bnd_rows, op->n_bnd, xk, ldx, xgk, ldg, yk, ldy, w); break;
+      case 8: rc = spmm_rows<8>(ctx, op, op->bnd_rows, op->n_bnd, xk, ldx, xgk, ldg, yk, ldy, w); break;
+      case 4: rc = spmm_rows<4>(ctx, op, op->bnd_rows, op->n_bnd, xk, ldx, xgk, ldg, yk, ldy, w); break;
+      case 2: rc = spmm_rows<2>(ctx, op, op->bnd_rows, op->n_bnd, xk, ldx, xgk, ldg, yk, ldy, w); break;
+      default: rc = spmm_rows<1>(ctx, op, op->bnd_rows, op->n_bnd, xk, ldx, xgk, ldg, yk, ldy, w); break;
     }
     if (rc) return rc;
     k0 += step;
