@@ -49,6 +49,19 @@ void b200_gmres_default_params(b200_gmres_params* p);
 int b200_belos_block_gmres_solve(b200_op* A, b200_mv* X, b200_mv* B, const b200_gmres_params* p,
                                  b200_gmres_result* r);
 
+/* The same driver with the solver manager chosen by name -- every one is the reference's own class
+ * template instantiated on <double, Belos::MultiVec<double>, Belos::Operator<double>>, so all of
+ * them run on the same kernels:
+ *   "BlockGmres"        belos/src/BelosBlockGmresSolMgr.hpp
+ *   "PseudoBlockGmres"  belos/src/BelosPseudoBlockGmresSolMgr.hpp  (block_size = number of systems
+ *                       advanced together; adaptive_block_size / flexible ignored)
+ *   "BlockCG"           belos/src/BelosBlockCGSolMgr.hpp           (num_blocks / max_restarts ignored)
+ *   "PseudoBlockCG"     belos/src/BelosPseudoBlockCGSolMgr.hpp     (also ignores block_size / ortho)
+ * Reference drivers: belos/epetra/test/BlockGmres/test_pseudo_bl_gmres_hb.cpp,
+ * belos/epetra/test/BlockCG/test_bl_cg_hb.cpp, test_pseudo_bl_cg_hb.cpp. */
+int b200_belos_solve(const char* solver, b200_op* A, b200_mv* X, b200_mv* B,
+                     const b200_gmres_params* p, b200_gmres_result* r);
+
 /* Runs Belos::TestMultiVecTraits and Belos::TestOperatorTraits (the reference's contract test)
  * on a B200MultiVec of n rows x ncols columns and a tridiagonal B200CrsOp. 0 = passed. */
 int b200_belos_mvop_test(b200_ctx* ctx, int n, int ncols, int verbose);

@@ -40,6 +40,15 @@ SOLVES_SMALL = [
     ("recirc2d_40_b16_dgks", "Recirc2D", (40, 40, 1), 16, 40, "DGKS", 1e-5, 200, 1000),
     ("brick3d_12_b8_icgs", "Brick3D", (12, 12, 12), 8, 30, "ICGS", 1e-8, 200),
 ]
+# other solver managers on the same kernels: (..., max iters, solver)
+SOLVES_MANAGERS = [
+    ("pseudo_gmres_laplace3d_12_b4_dgks", "Laplace3D", (12, 12, 12), 4, 40, "DGKS", 1e-8, 50, -1, "PseudoBlockGmres"),
+    ("pseudo_gmres_recirc2d_30_b3_icgs", "Recirc2D", (30, 30, 1), 3, 60, "ICGS", 1e-4, 100, -1, "PseudoBlockGmres"),
+    ("block_cg_laplace3d_12_b4_dgks", "Laplace3D", (12, 12, 12), 4, 1, "DGKS", 1e-8, 1, -1, "BlockCG"),
+    ("block_cg_laplace2d_40_b1_dgks", "Laplace2D", (40, 40, 1), 1, 1, "DGKS", 1e-8, 1, -1, "BlockCG"),
+    ("block_cg_brick3d_10_b2_icgs", "Brick3D", (10, 10, 10), 2, 1, "ICGS", 1e-8, 1, -1, "BlockCG"),
+    ("pseudo_cg_laplace3d_12_b4", "Laplace3D", (12, 12, 12), 4, 1, "DGKS", 1e-8, 1, -1, "PseudoBlockCG"),
+]
 SOLVES_FULL = [
     ("config1_laplace2d_100_b1_dgks", "Laplace2D", (100, 100, 1), 1, 50, "DGKS", 1e-8, 1000),
     ("config2_laplace3d_100_b4_dgks", "Laplace3D", (100, 100, 100), 4, 50, "DGKS", 1e-8, 1000),
@@ -107,13 +116,14 @@ def gen_solves(cases, fn, threads=1):
     for case in cases:
         label, name, dims, b, m, ortho, tol, maxr = case[:8]
         max_iters = case[8] if len(case) > 8 else -1
+        solver = case[9] if len(case) > 9 else "BlockGmres"
         kw = dict(conv=1.0, diff=1e-5) if name == "Recirc2D" else {}
         n, rp, ci, va = matrix(name, dims, **kw)
         xe, _ = ref.random(1, n, b)
         B = ref.apply(rp, ci, va, xe)
         X, r = ref.block_gmres(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=max_iters, max_restarts=maxr, tol=tol,
-                               ortho=ortho)
-        r.update(matrix=name, dims=list(dims), block_size=b, num_blocks=m, ortho=ortho, tol=tol, max_restarts=maxr, max_iters=max_iters,
+                               ortho=ortho, solver=solver)
+        r.update(matrix=name, dims=list(dims), block_size=b, num_blocks=m, ortho=ortho, tol=tol, max_restarts=maxr, max_iters=max_iters, solver=solver,
                  rhs="X_exact = Epetra LCG seed 1 (column-major sweep), B = A X_exact, X0 = 0",
                  max_abs_err=float(np.abs(X - xe).max()), threads=threads)
         res[label] = r
@@ -124,7 +134,9 @@ def gen_solves(cases, fn, threads=1):
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    if "--full" in sys.argv:
+    if "--managers" in sys.argv:
+        gen_solves(SOLVES_MANAGERS, "ref_solves_managers.json")
+    elif "--full" in sys.argv:
         gen_solves(SOLVES_FULL, "ref_solves_full.json", threads=1)
     else:
         gen_galeri()

@@ -152,7 +152,7 @@ def random(seed, n, k):
 
 
 def block_gmres(rowptr, colind, values, B, X0=None, block_size=1, num_blocks=300, max_iters=-1, max_restarts=20,
-                tol=1e-8, ortho="DGKS", adaptive_block_size=True, show_timers=False, verbosity=0):
+                tol=1e-8, ortho="DGKS", adaptive_block_size=True, show_timers=False, verbosity=0, solver="BlockGmres"):
     """Belos::BlockGmresSolMgr<double,Epetra_MultiVector,Epetra_Operator> on serial Epetra."""
     rp, ci, va = _csr(rowptr, colind, values)
     B = _F(B)
@@ -162,7 +162,7 @@ def block_gmres(rowptr, colind, values, B, X0=None, block_size=1, num_blocks=300
     p = GmresParams(block_size, num_blocks, max_iters, max_restarts, tol, o, verbosity, -1,
                     1 if adaptive_block_size else 0, 0, 1 if show_timers else 0)
     r = GmresResult()
-    _ck(lib().ref_block_gmres_csr(C.c_int64(n), _i32(rp), _i32(ci), _d(va), k, _d(B), C.c_int64(n), _d(X), C.c_int64(n),
+    _ck(lib().ref_belos_solve_csr(solver.encode(), C.c_int64(n), _i32(rp), _i32(ci), _d(va), k, _d(B), C.c_int64(n), _d(X), C.c_int64(n),
                                   C.byref(p), C.byref(r)))
     return X, dict(converged=bool(r.converged), num_iters=r.num_iters, achieved_tol=r.achieved_tol,
                    loss_of_accuracy=bool(r.loss_of_accuracy), solve_seconds=r.solve_seconds,

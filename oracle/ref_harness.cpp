@@ -19,7 +19,10 @@
 #include <string>
 #include <vector>
 
+#include "BelosBlockCGSolMgr.hpp"
 #include "BelosBlockGmresSolMgr.hpp"
+#include "BelosPseudoBlockCGSolMgr.hpp"
+#include "BelosPseudoBlockGmresSolMgr.hpp"
 #include "BelosConfigDefs.hpp"
 #include "BelosEpetraAdapter.hpp"
 #include "BelosLinearProblem.hpp"
@@ -244,11 +247,25 @@ extern "C" unsigned int ref_mv_random(unsigned int seed, int64_t n, int k, doubl
 }
 
 // Full reference solve on a CSR matrix (serial Epetra): X is initial guess in / solution out.
+extern "C" int ref_belos_solve_csr(const char* solver_name, int64_t n, const int32_t* rowptr,
+                                   const int32_t* colind, const double* values, int numrhs,
+                                   const double* Bh, int64_t ldb, double* Xh, int64_t ldx,
+                                   const ref_gmres_params* p, ref_gmres_result* r);
+
 extern "C" int ref_block_gmres_csr(int64_t n, const int32_t* rowptr, const int32_t* colind,
                                    const double* values, int numrhs, const double* Bh, int64_t ldb,
                                    double* Xh, int64_t ldx, const ref_gmres_params* p,
                                    ref_gmres_result* r) {
+  return ref_belos_solve_csr("BlockGmres", n, rowptr, colind, values, numrhs, Bh, ldb, Xh, ldx, p, r);
+}
+
+// the reference's solver managers on <double, Epetra_MultiVector, Epetra_Operator>, chosen by name
+extern "C" int ref_belos_solve_csr(const char* solver_name, int64_t n, const int32_t* rowptr,
+                                   const int32_t* colind, const double* values, int numrhs,
+                                   const double* Bh, int64_t ldb, double* Xh, int64_t ldx,
+                                   const ref_gmres_params* p, ref_gmres_result* r) {
   try {
+    const std::string which(solver_name ? solver_name : "");
     std::memset(r, 0, sizeof(*r));
     Epetra_SerialComm comm;
     Epetra_Map map((int)n, 0, comm);
@@ -278,14 +295,37 @@ extern "C" int ref_block_gmres_csr(int64_t n, const int32_t* rowptr, const int32
       return -1;
     }
     Teuchos::TimeMonitor::zeroOutTimers();
-    Belos::BlockGmresSolMgr<ST, MV, OP> solver(rcp(&problem, false), rcp(&belosList, false));
+    RCP<Belos::SolverManager<ST, MV, OP> > solver;
+    if (which == "BlockGmres") {
+      solver = rcp(new Belos::BlockGmresSolMgr<ST, MV, OP>(rcp(&problem, false), rcp(&belosList, false)));
+    } else if (which == "PseudoBlockGmres") {
+      belosList.remove("Adaptive Block Size");
+      belosList.remove("Flexible Gmres", false);
+      solver = rcp(new Belos::PseudoBlockGmresSolMgr<ST, MV, OP>(rcp(&problem, false), rcp(&belosList, false)));
+    } else if (which == "BlockCG") {
+      belosList.remove("Num Blocks");
+      belosList.remove("Maximum Restarts");
+      belosList.remove("Flexible Gmres", false);
+      solver = rcp(new Belos::BlockCGSolMgr<ST, MV, OP>(rcp(&problem, false), rcp(&belosList, false)));
+    } else if (which == "PseudoBlockCG") {
+      belosList.remove("Num Blocks");
+      belosList.remove("Maximum Restarts");
+      belosList.remove("Flexible Gmres", false);
+      belosList.remove("Block Size");
+      belosList.remove("Adaptive Block Size");
+      belosList.remove("Orthogonalization");
+      solver = rcp(new Belos::PseudoBlockCGSolMgr<ST, MV, OP>(rcp(&problem, false), rcp(&belosList, false)));
+    } else {
+      g_err = "unknown solver manager";
+      return -1;
+    }
     const auto t0 = std::chrono::steady_clock::now();
-    const Belos::ReturnType ret = solver.solve();
+    const Belos::ReturnType ret = solver->solve();
     const auto t1 = std::chrono::steady_clock::now();
     r->converged = (ret == Belos::Converged) ? 1 : 0;
-    r->num_iters = solver.getNumIters();
-    r->achieved_tol = solver.achievedTol();
-    r->loss_of_accuracy = solver.isLOADetected() ? 1 : 0;
+    r->num_iters = solver->getNumIters();
+    r->achieved_tol = solver->achievedTol();
+    r->loss_of_accuracy = solver->isLOADetected() ? 1 : 0;
     r->solve_seconds = std::chrono::duration<double>(t1 - t0).count();
     r->num_rhs = numrhs;
     std::vector<double> actual(numrhs), rhs(numrhs);

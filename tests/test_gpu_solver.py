@@ -16,6 +16,7 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 SOLVES = json.load(open(os.path.join(GOLD, "ref_solves.json")))
 FULL = json.load(open(os.path.join(GOLD, "ref_solves_full.json")))
+MANAGERS = json.load(open(os.path.join(GOLD, "ref_solves_managers.json")))
 
 
 @pytest.mark.parametrize("n,k", [(100, 5), (1000, 10), (37, 3)])
@@ -33,7 +34,7 @@ def run_case(ctx, g):
     B = tb.MultiVec(ctx, n, b)
     op.Apply(Xe, B)
     X = tb.MultiVec(ctx, n, b)
-    mgr = tb.BlockGmresSolMgr(op, block_size=b, num_blocks=g["num_blocks"], max_iters=g.get("max_iters", -1),
+    mgr = tb.SOLVER_MANAGERS[g.get("solver", "BlockGmres")](op, block_size=b, num_blocks=g["num_blocks"], max_iters=g.get("max_iters", -1),
                               max_restarts=g["max_restarts"], tol=g["tol"], ortho=g["ortho"])
     r = mgr.solve(X, B)
     return r, X.to_numpy(), xe
@@ -58,6 +59,18 @@ def test_iteration_count_parity_baseline_configs(ctx, label):
     assert max(r["true_rel_resid"]) <= g["tol"] * 1.001
     assert abs(r["num_iters"] - g["num_iters"]) <= max(1, round(0.02 * g["num_iters"])), (r["num_iters"], g["num_iters"])
     assert abs(r["achieved_tol"] - g["achieved_tol"]) <= 1e-3 * g["achieved_tol"] + 1e-12
+
+
+@pytest.mark.parametrize("label", sorted(MANAGERS))
+def test_other_solver_managers_iteration_parity(ctx, label):
+    """SURVEY 8 f.2: Belos::PseudoBlockGmresSolMgr / BlockCGSolMgr / PseudoBlockCGSolMgr (unmodified, instantiated on the
+    plugin classes) against the reference's Epetra runs of the same managers; same +-2 % iteration criterion."""
+    g = MANAGERS[label]
+    r, x, xe = run_case(ctx, g)
+    assert r["converged"]
+    assert max(r["true_rel_resid"]) <= g["tol"] * 1.001
+    assert abs(r["num_iters"] - g["num_iters"]) <= max(1, round(0.02 * g["num_iters"])), (r["num_iters"], g["num_iters"])
+    assert np.abs(x - xe).max() <= 10 * max(g["max_abs_err"], 1e-12)
 
 
 def test_known_answer_diagonal(ctx):

@@ -8,7 +8,10 @@
 #include <sstream>
 
 #include "B200BelosAdapter.hpp"
+#include "BelosBlockCGSolMgr.hpp"
 #include "BelosBlockGmresSolMgr.hpp"
+#include "BelosPseudoBlockCGSolMgr.hpp"
+#include "BelosPseudoBlockGmresSolMgr.hpp"
 #include "BelosLinearProblem.hpp"
 #include "BelosMVOPTester.hpp"
 #include "BelosOutputManager.hpp"
@@ -43,9 +46,20 @@ extern "C" void b200_gmres_default_params(b200_gmres_params* p) {
 
 extern "C" int b200_belos_block_gmres_solve(b200_op* A_h, b200_mv* X_h, b200_mv* B_h,
                                             const b200_gmres_params* p, b200_gmres_result* r) {
+  return b200_belos_solve("BlockGmres", A_h, X_h, B_h, p, r);
+}
+
+extern "C" int b200_belos_solve(const char* solver_name, b200_op* A_h, b200_mv* X_h, b200_mv* B_h,
+                                const b200_gmres_params* p, b200_gmres_result* r) {
   using Teuchos::RCP;
   using Teuchos::rcp;
-  if (!A_h || !X_h || !B_h || !p || !r) return b200::fail(B200_ERR_ARG, "solve: null argument");
+  if (!solver_name || !A_h || !X_h || !B_h || !p || !r)
+    return b200::fail(B200_ERR_ARG, "solve: null argument");
+  const std::string which(solver_name);
+  if (which != "BlockGmres" && which != "PseudoBlockGmres" && which != "BlockCG" &&
+      which != "PseudoBlockCG")
+    return b200::fail(B200_ERR_ARG,
+                      "solve: unknown solver manager (BlockGmres | PseudoBlockGmres | BlockCG | PseudoBlockCG)");
   std::memset(r, 0, sizeof(*r));
   try {
     // Non-owning views of the caller's handles: CloneView over all columns shares storage.
@@ -85,17 +99,39 @@ extern "C" int b200_belos_block_gmres_solve(b200_op* A_h, b200_mv* X_h, b200_mv*
       return b200::fail(B200_ERR_ARG, "Belos::LinearProblem failed to set up correctly");
 
     Teuchos::TimeMonitor::zeroOutTimers();
-    Belos::BlockGmresSolMgr<ST, MV, OP> solver(rcp(&problem, false), rcp(&belosList, false));
+    // every manager is the reference's own class template, instantiated on the plugin classes
+    RCP<Belos::SolverManager<ST, MV, OP> > solver;
+    RCP<Belos::LinearProblem<ST, MV, OP> > prob = rcp(&problem, false);
+    RCP<Teuchos::ParameterList> pl = rcp(&belosList, false);
+    if (which == "BlockGmres") {
+      solver = rcp(new Belos::BlockGmresSolMgr<ST, MV, OP>(prob, pl));
+    } else if (which == "PseudoBlockGmres") {
+      belosList.remove("Adaptive Block Size");
+      belosList.remove("Flexible Gmres", false);
+      solver = rcp(new Belos::PseudoBlockGmresSolMgr<ST, MV, OP>(prob, pl));
+    } else {
+      belosList.remove("Num Blocks");
+      belosList.remove("Maximum Restarts");
+      belosList.remove("Flexible Gmres", false);
+      if (which == "BlockCG") {
+        solver = rcp(new Belos::BlockCGSolMgr<ST, MV, OP>(prob, pl));
+      } else {
+        belosList.remove("Block Size");
+        belosList.remove("Adaptive Block Size");
+        belosList.remove("Orthogonalization");
+        solver = rcp(new Belos::PseudoBlockCGSolMgr<ST, MV, OP>(prob, pl));
+      }
+    }
     b200_ctx_sync(b200_mv_ctx(B_h));
     const auto t0 = std::chrono::steady_clock::now();
-    const Belos::ReturnType ret = solver.solve();
+    const Belos::ReturnType ret = solver->solve();
     b200_ctx_sync(b200_mv_ctx(B_h));
     const auto t1 = std::chrono::steady_clock::now();
 
     r->converged = (ret == Belos::Converged) ? 1 : 0;
-    r->num_iters = solver.getNumIters();
-    r->achieved_tol = solver.achievedTol();
-    r->loss_of_accuracy = solver.isLOADetected() ? 1 : 0;
+    r->num_iters = solver->getNumIters();
+    r->achieved_tol = solver->achievedTol();
+    r->loss_of_accuracy = solver->isLOADetected() ? 1 : 0;
     r->solve_seconds = std::chrono::duration<double>(t1 - t0).count();
     r->num_rhs = numrhs;
 

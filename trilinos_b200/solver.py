@@ -43,18 +43,21 @@ def solver_lib():
         _slib.b200_gmres_default_params.argtypes = [C.POINTER(GmresParams)]
         _slib.b200_belos_block_gmres_solve.argtypes = [vp, vp, vp, C.POINTER(GmresParams), C.POINTER(GmresResult)]
         _slib.b200_belos_block_gmres_solve.restype = C.c_int
+        _slib.b200_belos_solve.argtypes = [C.c_char_p, vp, vp, vp, C.POINTER(GmresParams), C.POINTER(GmresResult)]
+        _slib.b200_belos_solve.restype = C.c_int
         _slib.b200_belos_mvop_test.argtypes = [vp, C.c_int, C.c_int, C.c_int]
         _slib.b200_belos_mvop_test.restype = C.c_int
         _slib.b200_belos_timer_summary.argtypes = [C.c_char_p, C.c_int]
     return _slib
 
 
-SOLVER_EXPORTED = ("b200_gmres_default_params", "b200_belos_block_gmres_solve", "b200_belos_mvop_test",
+SOLVER_EXPORTED = ("b200_gmres_default_params", "b200_belos_block_gmres_solve", "b200_belos_solve", "b200_belos_mvop_test",
                    "b200_belos_timer_summary")
 
 
 class BlockGmresSolMgr:
     """Belos::BlockGmresSolMgr<double, Belos::MultiVec<double>, Belos::Operator<double>>."""
+    SOLVER = b"BlockGmres"
 
     def __init__(self, op, block_size=1, num_blocks=300, max_iters=1000, max_restarts=20, tol=1e-8,
                  ortho="DGKS", verbosity=0, output_frequency=-1, adaptive_block_size=True, flexible=False,
@@ -69,7 +72,7 @@ class BlockGmresSolMgr:
     def solve(self, X, B):
         """X: initial guess in / solution out; B: right-hand sides.  Returns a dict."""
         r = GmresResult()
-        rc = solver_lib().b200_belos_block_gmres_solve(self.op._h, X._h, B._h, C.byref(self.params), C.byref(r))
+        rc = solver_lib().b200_belos_solve(self.SOLVER, self.op._h, X._h, B._h, C.byref(self.params), C.byref(r))
         check(rc)
         self.result = dict(converged=bool(r.converged), num_iters=r.num_iters, achieved_tol=r.achieved_tol,
                            loss_of_accuracy=bool(r.loss_of_accuracy), solve_seconds=r.solve_seconds,
@@ -90,6 +93,26 @@ class BlockGmresSolMgr:
         buf = C.create_string_buffer(1 << 16)
         solver_lib().b200_belos_timer_summary(buf, len(buf))
         return buf.value.decode(errors="replace")
+
+
+class PseudoBlockGmresSolMgr(BlockGmresSolMgr):
+    """Belos::PseudoBlockGmresSolMgr (belos/src/BelosPseudoBlockGmresSolMgr.hpp): block_size independent
+    single-vector GMRES recurrences advanced together; the same plugin kernels."""
+    SOLVER = b"PseudoBlockGmres"
+
+
+class BlockCGSolMgr(BlockGmresSolMgr):
+    """Belos::BlockCGSolMgr (belos/src/BelosBlockCGSolMgr.hpp); num_blocks / max_restarts are ignored."""
+    SOLVER = b"BlockCG"
+
+
+class PseudoBlockCGSolMgr(BlockGmresSolMgr):
+    """Belos::PseudoBlockCGSolMgr (belos/src/BelosPseudoBlockCGSolMgr.hpp)."""
+    SOLVER = b"PseudoBlockCG"
+
+
+SOLVER_MANAGERS = {"BlockGmres": BlockGmresSolMgr, "PseudoBlockGmres": PseudoBlockGmresSolMgr,
+                   "BlockCG": BlockCGSolMgr, "PseudoBlockCG": PseudoBlockCGSolMgr}
 
 
 def mvop_test(ctx, n=100, ncols=5, verbose=False):
