@@ -309,9 +309,18 @@ def main():
     dom = max(kern, key=lambda k: kern[k]["ms"]) if kern else None
     roofline = None
     if dom:
+        # DRAM traffic of the dominant kernel: one `ncu --set full` capture at the mid-cycle shape (committed summary,
+        # profiles/ncu_traffic.json); per launch of that shape, next to its algorithmic bytes
+        traffic, traffic_detail = None, None
+        tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if wl == "laplace3d_100_b4" and os.path.exists(tp):
+            tj = json.load(open(tp))
+            if dom in tj.get("kernels", {}):
+                traffic_detail = dict(tj["kernels"][dom], source=tj.get("source"))
+                traffic = traffic_detail["dram_bytes"]
         roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
-                    "frac": kern[dom]["frac"], "traffic": None, "peak_source": peak_src,
-                    "launches": kern[dom]["calls"], "kernels": kern}
+                    "frac": kern[dom]["frac"], "traffic": traffic, "traffic_detail": traffic_detail,
+                    "peak_source": peak_src, "launches": kern[dom]["calls"], "kernels": kern}
 
     if rank == 0:
         out = {
