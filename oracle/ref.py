@@ -27,6 +27,13 @@ class GmresResult(C.Structure):
                 ("true_rel_resid", C.c_double * 64)]
 
 
+class ChebyParams(C.Structure):
+    """ifpack/src/Ifpack_Chebyshev.cpp:160-175 parameter names: degree, max eigenvalue (-1: power method), ratio
+    eigenvalue, min diagonal value, eigenvalue max iterations; seed pins the power method's start vector."""
+    _fields_ = [("degree", C.c_int), ("lambda_max", C.c_double), ("eig_ratio", C.c_double), ("min_diag", C.c_double),
+                ("eig_iters", C.c_int), ("seed", C.c_uint)]
+
+
 def available():
     return os.path.exists(SO)
 
@@ -164,6 +171,39 @@ def block_gmres(rowptr, colind, values, B, X0=None, block_size=1, num_blocks=300
     r = GmresResult()
     _ck(lib().ref_belos_solve_csr(solver.encode(), C.c_int64(n), _i32(rp), _i32(ci), _d(va), k, _d(B), C.c_int64(n), _d(X), C.c_int64(n),
                                   C.byref(p), C.byref(r)))
+    return X, dict(converged=bool(r.converged), num_iters=r.num_iters, achieved_tol=r.achieved_tol,
+                   loss_of_accuracy=bool(r.loss_of_accuracy), solve_seconds=r.solve_seconds,
+                   true_rel_resid=[r.true_rel_resid[i] for i in range(min(k, 64))])
+
+
+def cheby_apply(rowptr, colind, values, X, degree=3, lambda_max=-1.0, eig_ratio=30.0, min_diag=0.0, eig_iters=10, seed=1):
+    """Y = Ifpack_Chebyshev(A).ApplyInverse(X) (point mode, zero starting solution); returns (Y, lambda_max used)."""
+    rp, ci, va = _csr(rowptr, colind, values)
+    X = _F(X)
+    n, k = X.shape
+    Y = np.zeros((n, k), order="F")
+    cp = ChebyParams(degree, lambda_max, eig_ratio, min_diag, eig_iters, seed)
+    lam = C.c_double(0.0)
+    _ck(lib().ref_cheby_apply(C.c_int64(n), _i32(rp), _i32(ci), _d(va), C.byref(cp), _d(X), C.c_int64(n), k, _d(Y),
+                              C.c_int64(n), C.byref(lam)))
+    return Y, lam.value
+
+
+def belos_solve_cheby(rowptr, colind, values, B, cheby, X0=None, block_size=1, num_blocks=300, max_iters=-1,
+                      max_restarts=20, tol=1e-8, ortho="DGKS", solver="BlockGmres"):
+    """The reference's solver manager with Ifpack_Chebyshev as right preconditioner (Belos::EpetraPrecOp,
+    LinearProblem::setRightPrec).  cheby: dict(degree=, lambda_max=, eig_ratio=, min_diag=, eig_iters=, seed=)."""
+    rp, ci, va = _csr(rowptr, colind, values)
+    B = _F(B)
+    n, k = B.shape
+    X = np.zeros((n, k), order="F") if X0 is None else _F(X0).copy(order="F")
+    o = ortho.encode()
+    p = GmresParams(block_size, num_blocks, max_iters, max_restarts, tol, o, 0, -1, 1, 0, 0)
+    cp = ChebyParams(cheby.get("degree", 3), cheby.get("lambda_max", -1.0), cheby.get("eig_ratio", 30.0),
+                     cheby.get("min_diag", 0.0), cheby.get("eig_iters", 10), cheby.get("seed", 1))
+    r = GmresResult()
+    _ck(lib().ref_belos_solve_cheby_csr(solver.encode(), C.c_int64(n), _i32(rp), _i32(ci), _d(va), C.byref(cp), k, _d(B),
+                                        C.c_int64(n), _d(X), C.c_int64(n), C.byref(p), C.byref(r)))
     return X, dict(converged=bool(r.converged), num_iters=r.num_iters, achieved_tol=r.achieved_tol,
                    loss_of_accuracy=bool(r.loss_of_accuracy), solve_seconds=r.solve_seconds,
                    true_rel_resid=[r.true_rel_resid[i] for i in range(min(k, 64))])

@@ -31,8 +31,10 @@
 #include "Epetra_MultiVector.h"
 #include "Epetra_SerialComm.h"
 #include "Epetra_Util.h"
+#include "Epetra_Vector.h"
 #include "Galeri_CrsMatrices.h"
 #include "Galeri_Maps.h"
+#include "Ifpack_Chebyshev.h"
 #include "Teuchos_ParameterList.hpp"
 #include "Teuchos_RCP.hpp"
 #include "Teuchos_SerialDenseMatrix.hpp"
@@ -251,6 +253,12 @@ extern "C" int ref_belos_solve_csr(const char* solver_name, int64_t n, const int
                                    const int32_t* colind, const double* values, int numrhs,
                                    const double* Bh, int64_t ldb, double* Xh, int64_t ldx,
                                    const ref_gmres_params* p, ref_gmres_result* r);
+struct ref_cheby_params;
+static const ref_cheby_params* g_cheby = nullptr;  // set by ref_belos_solve_cheby_csr
+namespace {
+RCP<class Ifpack_Chebyshev> make_cheby(const RCP<Epetra_CrsMatrix>& A, const ref_cheby_params* c,
+                                       double* lambda_used);
+}
 
 extern "C" int ref_block_gmres_csr(int64_t n, const int32_t* rowptr, const int32_t* colind,
                                    const double* values, int numrhs, const double* Bh, int64_t ldb,
@@ -290,6 +298,11 @@ extern "C" int ref_belos_solve_csr(const char* solver_name, int64_t n, const int
     if (p->output_frequency > 0) belosList.set("Output Frequency", p->output_frequency);
 
     Belos::LinearProblem<ST, MV, OP> problem(A, X, B);
+    RCP<Ifpack_Chebyshev> cheb;
+    if (g_cheby) {  // right preconditioner, wrapped as the reference does (BelosEpetraAdapter.hpp:280-438)
+      cheb = make_cheby(Acrs, g_cheby, nullptr);
+      problem.setRightPrec(rcp(new Belos::EpetraPrecOp(cheb)));
+    }
     if (!problem.setProblem()) {
       g_err = "Belos::LinearProblem failed to set up correctly";
       return -1;
@@ -340,6 +353,70 @@ extern "C" int ref_belos_solve_csr(const char* solver_name, int64_t n, const int
   } catch (const std::exception& e) {
     return fail(e);
   }
+}
+
+// ---- Chebyshev right preconditioner: the reference's Ifpack_Chebyshev (ifpack/src/Ifpack_Chebyshev.cpp)
+// in point mode, zero starting solution.  lambda_max < 0: estimated by the reference's own power
+// method (Ifpack_Chebyshev::PowerMethod, :729-759) with an explicit RNG seed, then handed over as
+// "chebyshev: max eigenvalue" so the run is reproducible.
+struct ref_cheby_params {
+  int degree;
+  double lambda_max, eig_ratio, min_diag;
+  int eig_iters;
+  unsigned int seed;
+};
+
+namespace {
+RCP<Ifpack_Chebyshev> make_cheby(const RCP<Epetra_CrsMatrix>& A, const ref_cheby_params* c,
+                                 double* lambda_used) {
+  double lam = c->lambda_max;
+  if (lam < 0) {
+    Epetra_Vector invd(A->RowMap());
+    A->ExtractDiagonalCopy(invd);
+    for (int i = 0; i < invd.MyLength(); ++i)
+      invd[i] = (std::fabs(invd[i]) < c->min_diag) ? c->min_diag : 1.0 / invd[i];
+    unsigned int seed = c->seed;
+    if (Ifpack_Chebyshev::PowerMethod(*A, invd, c->eig_iters, lam, &seed) != 0)
+      throw std::runtime_error("Ifpack_Chebyshev::PowerMethod failed");
+  }
+  Teuchos::ParameterList pl;
+  pl.set("chebyshev: degree", c->degree);
+  pl.set("chebyshev: max eigenvalue", lam);
+  pl.set("chebyshev: ratio eigenvalue", c->eig_ratio);
+  pl.set("chebyshev: min diagonal value", c->min_diag);
+  pl.set("chebyshev: zero starting solution", true);
+  RCP<Ifpack_Chebyshev> P = rcp(new Ifpack_Chebyshev(A.get()));
+  if (P->SetParameters(pl) != 0 || P->Initialize() != 0 || P->Compute() != 0)
+    throw std::runtime_error("Ifpack_Chebyshev set-up failed");
+  if (lambda_used) *lambda_used = lam;
+  return P;
+}
+}  // namespace
+
+extern "C" int ref_cheby_apply(int64_t n, const int32_t* rowptr, const int32_t* colind,
+                               const double* values, const ref_cheby_params* c, const double* X,
+                               int64_t ldx, int k, double* Y, int64_t ldy, double* lambda_used) {
+  try {
+    Epetra_SerialComm comm;
+    Epetra_Map map((int)n, 0, comm);
+    RCP<Epetra_CrsMatrix> A = csr_to_epetra(map, n, rowptr, colind, values);
+    RCP<Ifpack_Chebyshev> P = make_cheby(A, c, lambda_used);
+    MV x = view(map, X, ldx, k), y = view(map, Y, ldy, k);
+    return P->ApplyInverse(x, y);
+  } catch (const std::exception& e) {
+    return fail(e);
+  }
+}
+
+extern "C" int ref_belos_solve_cheby_csr(const char* solver_name, int64_t n, const int32_t* rowptr,
+                                         const int32_t* colind, const double* values,
+                                         const ref_cheby_params* c, int numrhs, const double* Bh,
+                                         int64_t ldb, double* Xh, int64_t ldx,
+                                         const ref_gmres_params* p, ref_gmres_result* r) {
+  g_cheby = c;
+  const int rc = ref_belos_solve_csr(solver_name, n, rowptr, colind, values, numrhs, Bh, ldb, Xh, ldx, p, r);
+  g_cheby = nullptr;
+  return rc;
 }
 
 extern "C" int ref_timer_summary(char* buf, int buflen) {
