@@ -200,6 +200,36 @@ class B200CrsOp : public Operator<double> {
   bool own_;
 };
 
+/// Chebyshev smoother (the reference's Ifpack_Chebyshev, point mode) as a Belos::Operator whose
+/// Apply is ApplyInverse -- the role Belos::EpetraPrecOp plays for Epetra preconditioners
+/// (belos/epetra/src/BelosEpetraAdapter.hpp:280-438), to be handed to
+/// LinearProblem::setRightPrec / setLeftPrec.
+class B200ChebyshevOp : public Operator<double> {
+ public:
+  explicit B200ChebyshevOp(b200_cheby* c, bool own = false) : c_(c), own_(own) {}
+  ~B200ChebyshevOp() override {
+    if (own_) b200_cheby_destroy(c_);
+  }
+  void Apply(const MultiVec<double>& x, MultiVec<double>& y, ETrans trans = NOTRANS) const override {
+    const B200MultiVec* vx = dynamic_cast<const B200MultiVec*>(&x);
+    B200MultiVec* vy = dynamic_cast<B200MultiVec*>(&y);
+    TEUCHOS_TEST_FOR_EXCEPTION(vx == nullptr || vy == nullptr, B200OpFailure,
+                               "Belos::B200ChebyshevOp::Apply: x and/or y could not be dynamic "
+                               "cast to a Belos::B200MultiVec.");
+    TEUCHOS_TEST_FOR_EXCEPTION(trans != NOTRANS, B200OpFailure,
+                               "Belos::B200ChebyshevOp::Apply: transpose is not available.");
+    const int info = b200_cheby_apply(c_, vx->handle(), vy->handle());
+    TEUCHOS_TEST_FOR_EXCEPTION(info != 0, B200OpFailure,
+                               "Belos::B200ChebyshevOp::Apply: b200_cheby_apply returned a nonzero "
+                               "error code of " << info << ": " << b200_last_error());
+  }
+  bool HasApplyTranspose() const override { return false; }
+
+ private:
+  b200_cheby* c_;
+  bool own_;
+};
+
 }  // namespace Belos
 
 #endif

@@ -193,6 +193,36 @@ int b200_galeri_generate(const char* name, int nx, int ny, int nz, double conv, 
                          int64_t row_begin, int64_t row_end, int64_t* nnz, int32_t* rowptr,
                          int64_t* colind_global, double* values);
 
+/* ---- right preconditioning through the same boundary -------------
+ * Element-wise product with a broadcast vector: mv(:,j) = scalar_this*mv(:,j) + scalar_ab * A(:,0) .* B(:,j)
+ * Epetra_MultiVector::Multiply(double ScalarAB, A, B, double ScalarThis) with a single-vector A
+ * (epetra/src/Epetra_MultiVector.cpp; scalar_this == 0 never reads mv).  B may alias mv. */
+int b200_mv_multiply_elementwise(b200_mv* mv, double scalar_ab, const b200_mv* A, const b200_mv* B,
+                                 double scalar_this);
+/* Epetra_CrsMatrix::ExtractDiagonalCopy: a new one-column multivector on the operator's row map. */
+int b200_op_extract_diagonal(const b200_op* op, b200_mv** diag);
+
+/* Chebyshev polynomial smoother in D^-1 A, the reference's Ifpack_Chebyshev in point mode with a
+ * zero starting solution (ifpack/src/Ifpack_Chebyshev.cpp: SetParameters :160-205, Compute
+ * :283-372, ApplyInverse :466-725, PowerMethod :729-759).  Fields follow the ParameterList keys
+ * "chebyshev: degree", ": max eigenvalue" (< 0: estimated by the power method with eig_iters
+ * iterations from a start vector drawn with `seed`), ": ratio eigenvalue", ": min diagonal
+ * value", ": eigenvalue max iterations". */
+typedef struct b200_cheby b200_cheby;
+typedef struct {
+  int degree;
+  double lambda_max, eig_ratio, min_diag;
+  int eig_iters;
+  unsigned int seed;
+} b200_cheby_params;
+void b200_cheby_default_params(b200_cheby_params* p); /* 1, -1, 30, 0, 10, 1 (Ifpack defaults) */
+/* constructor + SetParameters + Initialize + Compute; the operator must outlive the smoother */
+int b200_cheby_create(b200_op* op, const b200_cheby_params* p, b200_cheby** out);
+/* ApplyInverse: y = p(D^-1 A) D^-1 x; x and y are n x k multivectors of the operator's map */
+int b200_cheby_apply(b200_cheby* c, const b200_mv* x, b200_mv* y);
+int b200_cheby_lambda(const b200_cheby* c, double* lambda_max, double* lambda_min);
+int b200_cheby_destroy(b200_cheby* c);
+
 #ifdef __cplusplus
 }
 #endif

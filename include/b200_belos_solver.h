@@ -62,6 +62,13 @@ int b200_belos_block_gmres_solve(b200_op* A, b200_mv* X, b200_mv* B, const b200_
 int b200_belos_solve(const char* solver, b200_op* A, b200_mv* X, b200_mv* B,
                      const b200_gmres_params* p, b200_gmres_result* r);
 
+/* The same with a Chebyshev smoother (b200_cheby, include/b200_belos.h) as preconditioner:
+ * LinearProblem::setRightPrec (left == 0; belos/src/BelosLinearProblem.hpp:1057-1071) or setLeftPrec,
+ * wrapped as Belos::B200ChebyshevOp the way the reference wraps Ifpack objects in
+ * Belos::EpetraPrecOp (belos/epetra/src/BelosEpetraAdapter.hpp:280-438).  prec == NULL: none. */
+int b200_belos_solve_prec(const char* solver, b200_op* A, b200_cheby* prec, int left, b200_mv* X,
+                          b200_mv* B, const b200_gmres_params* p, b200_gmres_result* r);
+
 /* Runs Belos::TestMultiVecTraits and Belos::TestOperatorTraits (the reference's contract test)
  * on a B200MultiVec of n rows x ncols columns and a tridiagonal B200CrsOp. 0 = passed. */
 int b200_belos_mvop_test(b200_ctx* ctx, int n, int ncols, int verbose);

@@ -109,6 +109,52 @@ def gen_kernels():
     print("wrote", fn)
 
 
+# Chebyshev smoother / right preconditioner: the reference's Ifpack_Chebyshev
+CHEBY_APPLY = [  # (label, matrix, dims, k, degree, lambda_max (-1: power method, seed 1), ratio)
+    ("laplace3d_7x6x5_k1_d3", "Laplace3D", (7, 6, 5), 1, 3, -1.0, 30.0),
+    ("laplace3d_7x6x5_k3_d5", "Laplace3D", (7, 6, 5), 3, 5, -1.0, 30.0),
+    ("laplace2d_10x8_k4_d1", "Laplace2D", (10, 8, 1), 4, 1, 1.9, 20.0),
+    ("recirc2d_12x9_k2_d4", "Recirc2D", (12, 9, 1), 2, 4, 2.5, 30.0),
+    ("laplace3d_20_k4_d8", "Laplace3D", (20, 20, 20), 4, 8, -1.0, 30.0),
+]
+# (label, matrix, dims, block size, num blocks, ortho, tol, max restarts, solver, cheby dict)
+SOLVES_PREC = [
+    ("gmres_laplace3d_12_b4_cheb4", "Laplace3D", (12, 12, 12), 4, 40, "DGKS", 1e-8, 50, "BlockGmres", dict(degree=4)),
+    ("gmres_laplace3d_20_b4_cheb8", "Laplace3D", (20, 20, 20), 4, 50, "DGKS", 1e-8, 50, "BlockGmres", dict(degree=8)),
+    ("gmres_laplace2d_40_b1_cheb3", "Laplace2D", (40, 40, 1), 1, 30, "ICGS", 1e-8, 200, "BlockGmres", dict(degree=3, lambda_max=2.0)),
+    ("pseudo_gmres_laplace3d_12_b2_cheb2", "Laplace3D", (12, 12, 12), 2, 40, "DGKS", 1e-8, 50, "PseudoBlockGmres", dict(degree=2)),
+    ("block_cg_laplace3d_12_b4_cheb3", "Laplace3D", (12, 12, 12), 4, 1, "DGKS", 1e-8, 1, "BlockCG", dict(degree=3)),
+]
+
+
+def gen_cheby():
+    out = {}
+    for label, name, dims, k, degree, lam, ratio in CHEBY_APPLY:
+        kw = dict(conv=1.0, diff=1e-5) if name == "Recirc2D" else {}
+        n, rp, ci, va = matrix(name, dims, **kw)
+        X, _ = ref.random(7, n, k)
+        Y, lam_used = ref.cheby_apply(rp, ci, va, X, degree=degree, lambda_max=lam, eig_ratio=ratio, seed=1)
+        out[label + "_X"] = X
+        out[label + "_Y"] = Y
+        out[label + "_lambda"] = lam_used
+        print(label, lam_used, float(np.linalg.norm(Y)))
+    np.savez_compressed(os.path.join(OUT, "ref_cheby.npz"), **out)
+    path = os.path.join(OUT, "ref_solves_prec.json")
+    res = {}
+    for label, name, dims, b, m, ortho, tol, maxr, solver, ch in SOLVES_PREC:
+        n, rp, ci, va = matrix(name, dims)
+        xe, _ = ref.random(1, n, b)
+        B = ref.apply(rp, ci, va, xe)
+        X, r = ref.belos_solve_cheby(rp, ci, va, B, ch, block_size=b, num_blocks=m, max_restarts=maxr, tol=tol, ortho=ortho,
+                                     solver=solver)
+        r.update(matrix=name, dims=list(dims), block_size=b, num_blocks=m, ortho=ortho, tol=tol, max_restarts=maxr, max_iters=-1,
+                 solver=solver, cheby=ch, max_abs_err=float(np.abs(X - xe).max()),
+                 rhs="X_exact = Epetra LCG seed 1, B = A X_exact, X0 = 0; right preconditioner Ifpack_Chebyshev")
+        res[label] = r
+        print(label, r["num_iters"], r["converged"], max(r["true_rel_resid"]), flush=True)
+    json.dump(res, open(path, "w"), indent=1, sort_keys=True)
+
+
 def gen_solves(cases, fn, threads=1):
     path = os.path.join(OUT, fn)
     res = json.load(open(path)) if os.path.exists(path) else {}
@@ -134,7 +180,9 @@ def gen_solves(cases, fn, threads=1):
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    if "--managers" in sys.argv:
+    if "--cheby" in sys.argv:
+        gen_cheby()
+    elif "--managers" in sys.argv:
         gen_solves(SOLVES_MANAGERS, "ref_solves_managers.json")
     elif "--full" in sys.argv:
         gen_solves(SOLVES_FULL, "ref_solves_full.json", threads=1)

@@ -79,6 +79,13 @@ _SIGS = {
     "b200_op_destroy": (C.c_int, [vp]),
     "b200_op_apply": (C.c_int, [vp, vp, vp, C.c_int]),
     "b200_op_info": (C.c_int, [vp, P(c_i64), P(c_i64), P(c_i64), P(c_i64), P(c_i64)]),
+    "b200_mv_multiply_elementwise": (C.c_int, [vp, c_dbl, vp, vp, c_dbl]),
+    "b200_op_extract_diagonal": (C.c_int, [vp, P(vp)]),
+    "b200_cheby_default_params": (None, [vp]),
+    "b200_cheby_create": (C.c_int, [vp, vp, P(vp)]),
+    "b200_cheby_apply": (C.c_int, [vp, vp, vp]),
+    "b200_cheby_lambda": (C.c_int, [vp, P(c_dbl), P(c_dbl)]),
+    "b200_cheby_destroy": (C.c_int, [vp]),
     "b200_linear_partition": (C.c_int, [c_i64, C.c_int, C.c_int, P(c_i64), P(c_i64)]),
     "b200_build_colmap": (c_i64, [c_i64, C.c_int, C.c_int, c_i64, P(c_i64), P(c_i32), P(c_i64), P(c_i32)]),
     "b200_halo_recv_plan": (C.c_int, [C.c_int, c_i64, P(c_i32), P(c_i64), P(c_i64)]),

@@ -111,6 +111,10 @@ class MultiVec:
         check(lib.b200_mv_create(ctx._h, n_local, ng, row_offset, ncols, 1 if zero else 0, C.byref(h)))
         self._h = h
 
+    def Multiply(self, scalar_ab, A, B, scalar_this):
+        """Epetra_MultiVector::Multiply(ScalarAB, A, B, ScalarThis), element-wise, A a single vector."""
+        check(lib.b200_mv_multiply_elementwise(self._h, scalar_ab, A._h, B._h, scalar_this))
+
     @classmethod
     def from_numpy(cls, ctx, a, n_global=None, row_offset=0):
         a = np.asfortranarray(np.atleast_2d(a.T).T if a.ndim == 1 else a, dtype=np.float64)
@@ -227,6 +231,43 @@ class MultiVec:
             check(lib.b200_mv_copy_from_host(self._h, _dptr(a), max(n, 1)))
 
 
+class ChebyParams(C.Structure):
+    """include/b200_belos.h b200_cheby_params (Ifpack_Chebyshev ParameterList keys)."""
+    _fields_ = [("degree", C.c_int), ("lambda_max", c_dbl), ("eig_ratio", c_dbl), ("min_diag", c_dbl),
+                ("eig_iters", C.c_int), ("seed", C.c_uint)]
+
+
+class Chebyshev:
+    """Chebyshev smoother in D^-1 A: the reference's Ifpack_Chebyshev (point mode, zero starting solution;
+    ifpack/src/Ifpack_Chebyshev.cpp) on the B200 kernels.  Apply == ApplyInverse, so the object is used as a
+    Belos::Operator preconditioner (Belos::EpetraPrecOp's role)."""
+
+    def __init__(self, op, degree=1, lambda_max=-1.0, eig_ratio=30.0, min_diag=0.0, eig_iters=10, seed=1):
+        self.op = op  # must outlive the smoother
+        self.params = ChebyParams(degree, lambda_max, eig_ratio, min_diag, eig_iters, seed)
+        h = vp()
+        check(lib.b200_cheby_create(op._h, C.byref(self.params), C.byref(h)))
+        self._h = h
+
+    def __del__(self):
+        try:
+            if self._h:
+                lib.b200_cheby_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def ApplyInverse(self, x, y):
+        check(lib.b200_cheby_apply(self._h, x._h, y._h))
+
+    Apply = ApplyInverse
+
+    def lambdas(self):
+        a, b = c_dbl(), c_dbl()
+        check(lib.b200_cheby_lambda(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+
 class CrsOperator:
     """Belos::Operator<double> over a row-block CSR matrix (replaces Belos::EpetraOp over
     Epetra_CrsMatrix)."""
@@ -255,6 +296,12 @@ class CrsOperator:
 
     def HasApplyTranspose(self):
         return False
+
+    def ExtractDiagonalCopy(self):
+        """Epetra_CrsMatrix::ExtractDiagonalCopy -> one-column MultiVec on the row map."""
+        h = vp()
+        check(lib.b200_op_extract_diagonal(self._h, C.byref(h)))
+        return MultiVec(self.ctx, 0, 1, _h=h)
 
     def info(self):
         v = [c_i64() for _ in range(5)]

@@ -51,6 +51,12 @@ extern "C" int b200_belos_block_gmres_solve(b200_op* A_h, b200_mv* X_h, b200_mv*
 
 extern "C" int b200_belos_solve(const char* solver_name, b200_op* A_h, b200_mv* X_h, b200_mv* B_h,
                                 const b200_gmres_params* p, b200_gmres_result* r) {
+  return b200_belos_solve_prec(solver_name, A_h, nullptr, 0, X_h, B_h, p, r);
+}
+
+extern "C" int b200_belos_solve_prec(const char* solver_name, b200_op* A_h, b200_cheby* prec,
+                                     int left, b200_mv* X_h, b200_mv* B_h,
+                                     const b200_gmres_params* p, b200_gmres_result* r) {
   using Teuchos::RCP;
   using Teuchos::rcp;
   if (!solver_name || !A_h || !X_h || !B_h || !p || !r)
@@ -95,6 +101,10 @@ extern "C" int b200_belos_solve(const char* solver_name, b200_op* A_h, b200_mv* 
     if (p->output_frequency > 0) belosList.set("Output Frequency", p->output_frequency);
 
     Belos::LinearProblem<ST, MV, OP> problem(A, X, B);
+    if (prec) {  // BelosLinearProblem.hpp:1057-1071 (right) / :1040-1056 (left)
+      RCP<OP> M = rcp(new Belos::B200ChebyshevOp(prec, false));
+      if (left) problem.setLeftPrec(M); else problem.setRightPrec(M);
+    }
     if (!problem.setProblem())
       return b200::fail(B200_ERR_ARG, "Belos::LinearProblem failed to set up correctly");
 

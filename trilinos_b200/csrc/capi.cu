@@ -948,3 +948,179 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
   if (xtmp) b200_mv_destroy(xtmp);
   return rc;
 }
+
+// =========================================================================== preconditioning
+extern "C" int b200_mv_multiply_elementwise(b200_mv* mv, double scalar_ab, const b200_mv* A,
+                                            const b200_mv* B, double scalar_this) {
+  if (!mv || !A || !B) return fail(B200_ERR_ARG, "Multiply: null multivector");
+  if (A->ncols() != 1)
+    return fail(B200_ERR_ARG, "Multiply: A must be a single vector (broadcast over the columns)");
+  if (B->ncols() != mv->ncols())
+    return fail(B200_ERR_ARG, "Multiply: number of vectors differs (Epetra Multiply: -1)");
+  if (!same_map(mv, A) || !same_map(mv, B))
+    return fail(B200_ERR_SHAPE, "Multiply: vector lengths differ (Epetra Multiply: -2)");
+  Ctx* ctx = mv->ctx;
+  const int k = mv->ncols();
+  for (int j = 0; j < k;) {
+    const int len = run_length(j, k, mv, j, B, j);
+    B200_TRY(launch_ewise_mul(ctx, mv->col(j), mv->ld, A->col(0), B->col(j), B->ld, mv->n_local, len,
+                              scalar_ab, scalar_this));
+    mv->touch(j, len);
+    j += len;
+  }
+  return 0;
+}
+
+extern "C" int b200_op_extract_diagonal(const b200_op* op, b200_mv** diag) {
+  if (!op || !diag) return fail(B200_ERR_ARG, "ExtractDiagonalCopy: null argument");
+  B200_TRY(new_mv(op->ctx, op->n_local, op->n_global, op->row_begin, 1, diag));
+  return launch_diag(op->ctx, op, (*diag)->col(0), false, 0.0);
+}
+
+struct b200_cheby {
+  b200_op* op = nullptr;
+  b200_cheby_params p;
+  b200_mv* invd = nullptr;      // guarded reciprocal of the diagonal
+  double lambda_max = 0.0, lambda_min = 0.0;
+  b200_mv *W = nullptr, *V = nullptr;  // work blocks, kept for the last block width
+};
+
+extern "C" void b200_cheby_default_params(b200_cheby_params* p) {
+  if (!p) return;
+  p->degree = 1;
+  p->lambda_max = -1.0;
+  p->eig_ratio = 30.0;
+  p->min_diag = 0.0;
+  p->eig_iters = 10;
+  p->seed = 1;
+}
+
+extern "C" int b200_cheby_destroy(b200_cheby* c) {
+  if (!c) return 0;
+  b200_mv_destroy(c->invd);
+  b200_mv_destroy(c->W);
+  b200_mv_destroy(c->V);
+  delete c;
+  return 0;
+}
+
+extern "C" int b200_cheby_create(b200_op* op, const b200_cheby_params* p, b200_cheby** out) {
+  if (!op || !p || !out) return fail(B200_ERR_ARG, "b200_cheby_create: null argument");
+  if (p->degree <= 0)  // Ifpack_Chebyshev::Compute: "at least one application" (-2)
+    return fail(B200_ERR_ARG, "b200_cheby_create: polynomial degree must be >= 1");
+  Ctx* ctx = op->ctx;
+  auto* c = new b200_cheby();
+  c->op = op;
+  c->p = *p;
+  int rc = new_mv(ctx, op->n_local, op->n_global, op->row_begin, 1, &c->invd);
+  if (!rc) rc = launch_diag(ctx, op, c->invd->col(0), true, p->min_diag);
+  double lam = p->lambda_max;
+  if (!rc && lam < 0) {
+    // Ifpack_Chebyshev::PowerMethod (:729-759) on D^-1 A, start vector from the Epetra LCG
+    b200_mv *x = nullptr, *y = nullptr;
+    rc = new_mv(ctx, op->n_local, op->n_global, op->row_begin, 1, &x);
+    if (!rc) rc = new_mv(ctx, op->n_local, op->n_global, op->row_begin, 1, &y);
+    const unsigned int saved = ctx->seed;
+    if (!rc) rc = b200_ctx_set_seed(static_cast<b200_ctx*>(ctx), p->seed);
+    if (!rc) rc = b200_mv_random(x);
+    ctx->seed = saved;
+    double norm = 0.0, top = 0.0, bot = 0.0;
+    if (!rc) rc = b200_mv_norm(x, B200_NORM_TWO, &norm, 1);
+    if (!rc && norm == 0.0) rc = fail(B200_ERR_ARG, "power method: zero start vector");
+    if (!rc) rc = b200_mv_scale(x, 1.0 / norm);
+    lam = 0.0;
+    for (int it = 0; it < p->eig_iters && !rc; ++it) {
+      rc = b200_op_apply(op, x, y, 0);
+      if (!rc) rc = b200_mv_multiply_elementwise(y, 1.0, c->invd, y, 0.0);
+      if (!rc) rc = b200_mv_dot(y, x, &top, 1);
+      if (!rc) rc = b200_mv_dot(x, x, &bot, 1);
+      lam = top / bot;
+      if (!rc) rc = b200_mv_norm(y, B200_NORM_TWO, &norm, 1);
+      if (!rc && norm == 0.0) rc = fail(B200_ERR_ARG, "power method: zero iterate");
+      if (!rc) rc = b200_mv_add_mv(x, 1.0 / norm, y, 0.0, y);
+    }
+    b200_mv_destroy(x);
+    b200_mv_destroy(y);
+  }
+  if (rc) {
+    b200_cheby_destroy(c);
+    return rc;
+  }
+  // Compute(): "Test for Exact Preconditioned case"
+  if (std::fabs(lam - 1.0) < 1e-6) {
+    c->lambda_max = c->lambda_min = 1.0;
+  } else {
+    c->lambda_max = lam;
+    c->lambda_min = lam / p->eig_ratio;
+  }
+  *out = c;
+  return 0;
+}
+
+extern "C" int b200_cheby_lambda(const b200_cheby* c, double* lambda_max, double* lambda_min) {
+  if (!c) return fail(B200_ERR_ARG, "b200_cheby_lambda: null smoother");
+  if (lambda_max) *lambda_max = c->lambda_max;
+  if (lambda_min) *lambda_min = c->lambda_min;
+  return 0;
+}
+
+extern "C" int b200_cheby_apply(b200_cheby* c, const b200_mv* x, b200_mv* y) {
+  if (!c || !x || !y) return fail(B200_ERR_ARG, "b200_cheby_apply: null argument");
+  if (x->ncols() != y->ncols()) return fail(B200_ERR_ARG, "ApplyInverse: number of vectors differs (-2)");
+  if (!same_map(x, y) || x->n_local != c->op->n_local)
+    return fail(B200_ERR_SHAPE, "ApplyInverse: vector lengths differ from the operator's map");
+  Ctx* ctx = x->ctx;
+  const int k = x->ncols();
+  if (k == 0) return 0;
+  // AztecOO-style aliasing (x and y the same memory): work on a copy of x, as :482-488
+  b200_mv* xcopy = nullptr;
+  if (columns_overlap(x, y)) {
+    B200_TRY(b200_mv_clone_copy(x, nullptr, 0, &xcopy));
+    x = xcopy;
+  }
+  int rc = 0;
+  const double* invd = c->invd->col(0);
+  const int64_t n = x->n_local;
+  if (c->lambda_min == 1.0 && c->lambda_max == c->lambda_min) {  // identity case :505-525
+    rc = b200_mv_multiply_elementwise(y, 1.0, c->invd, x, 0.0);
+    if (xcopy) b200_mv_destroy(xcopy);
+    return rc;
+  }
+  if (!c->W || c->W->ncols() != k) {
+    b200_mv_destroy(c->W);
+    b200_mv_destroy(c->V);
+    c->W = c->V = nullptr;
+    rc = new_mv(ctx, x->n_local, x->n_global, x->row_offset, k, &c->W);
+    if (!rc) rc = new_mv(ctx, x->n_local, x->n_global, x->row_offset, k, &c->V);
+  }
+  // coefficients :529-533 (delta is the inverse of ML_Cheby's)
+  const double alpha = c->lambda_max / c->p.eig_ratio;
+  const double beta = 1.1 * c->lambda_max;
+  const double delta = 2.0 / (beta - alpha);
+  const double theta = 0.5 * (beta + alpha);
+  const double s1 = theta * delta;
+  const double oot = 1.0 / theta;
+  for (int j = 0; j < k && !rc;) {
+    const int len = run_length(j, k, x, j, y, j);
+    rc = launch_cheby_first(ctx, c->W->col(j), c->W->ld, y->col(j), y->ld, invd, x->col(j), x->ld, n,
+                            len, oot, k == 1);
+    j += len;
+  }
+  y->touch(0, k);
+  double rhok = 1.0 / s1;
+  for (int it = 0; it < c->p.degree - 1 && !rc; ++it) {
+    rc = b200_op_apply(c->op, y, c->V, 0);
+    const double rhokp1 = 1.0 / (2.0 * s1 - rhok);
+    const double d1 = rhokp1 * rhok, d2 = 2.0 * rhokp1 * delta;
+    rhok = rhokp1;
+    for (int j = 0; j < k && !rc;) {
+      const int len = run_length(j, k, x, j, y, j);
+      rc = launch_cheby_step(ctx, c->W->col(j), c->W->ld, y->col(j), y->ld, invd, x->col(j), x->ld,
+                             c->V->col(j), c->V->ld, n, len, d1, d2);
+      j += len;
+    }
+    y->touch(0, k);
+  }
+  if (xcopy) b200_mv_destroy(xcopy);
+  return rc;
+}

@@ -262,6 +262,17 @@ struct Op {
 // ---- kernel launchers (defined in the .cu files) ---------------------------------
 // elementwise.cu
 int launch_fill(Ctx*, double* y, int64_t ld, int64_t n, int k, double a);
+// y(:,j) = sthis*y(:,j) + sab * d(:) .* b(:,j)   (d: one column)
+int launch_ewise_mul(Ctx*, double* y, int64_t ldy, const double* d, const double* b, int64_t ldb,
+                     int64_t n, int k, double sab, double sthis);
+// Chebyshev smoother passes (Ifpack_Chebyshev::ApplyInverse arithmetic)
+int launch_cheby_first(Ctx*, double* w, int64_t ldw, double* y, int64_t ldy, const double* invd,
+                       const double* x, int64_t ldx, int64_t n, int k, double oot, bool single);
+int launch_cheby_step(Ctx*, double* w, int64_t ldw, double* y, int64_t ldy, const double* invd,
+                      const double* x, int64_t ldx, const double* v, int64_t ldv, int64_t n, int k,
+                      double d1, double d2);
+struct Op;
+int launch_diag(Ctx*, const Op* op, double* out, bool invert, double min_diag);
 int launch_axpby(Ctx*, double* y, int64_t ldy, const double* a, int64_t lda, const double* b,
                  int64_t ldb, int64_t n, int k, double alpha, double beta);
 int launch_scale_cols(Ctx*, double* y, int64_t ld, int64_t n, int k, const double* alpha_host);

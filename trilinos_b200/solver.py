@@ -45,13 +45,16 @@ def solver_lib():
         _slib.b200_belos_block_gmres_solve.restype = C.c_int
         _slib.b200_belos_solve.argtypes = [C.c_char_p, vp, vp, vp, C.POINTER(GmresParams), C.POINTER(GmresResult)]
         _slib.b200_belos_solve.restype = C.c_int
+        _slib.b200_belos_solve_prec.argtypes = [C.c_char_p, vp, vp, C.c_int, vp, vp, C.POINTER(GmresParams),
+                                                C.POINTER(GmresResult)]
+        _slib.b200_belos_solve_prec.restype = C.c_int
         _slib.b200_belos_mvop_test.argtypes = [vp, C.c_int, C.c_int, C.c_int]
         _slib.b200_belos_mvop_test.restype = C.c_int
         _slib.b200_belos_timer_summary.argtypes = [C.c_char_p, C.c_int]
     return _slib
 
 
-SOLVER_EXPORTED = ("b200_gmres_default_params", "b200_belos_block_gmres_solve", "b200_belos_solve", "b200_belos_mvop_test",
+SOLVER_EXPORTED = ("b200_gmres_default_params", "b200_belos_block_gmres_solve", "b200_belos_solve", "b200_belos_solve_prec", "b200_belos_mvop_test",
                    "b200_belos_timer_summary")
 
 
@@ -61,8 +64,10 @@ class BlockGmresSolMgr:
 
     def __init__(self, op, block_size=1, num_blocks=300, max_iters=1000, max_restarts=20, tol=1e-8,
                  ortho="DGKS", verbosity=0, output_frequency=-1, adaptive_block_size=True, flexible=False,
-                 show_timers=False):
+                 show_timers=False, right_prec=None, left_prec=None):
         self.op = op
+        # LinearProblem::setRightPrec / setLeftPrec with a trilinos_b200.Chebyshev
+        self.prec, self.left = (left_prec, 1) if left_prec is not None else (right_prec, 0)
         self._ortho = ortho.encode()
         self.params = GmresParams(block_size, num_blocks, max_iters, max_restarts, tol, self._ortho, verbosity,
                                   output_frequency, 1 if adaptive_block_size else 0, 1 if flexible else 0,
@@ -72,7 +77,8 @@ class BlockGmresSolMgr:
     def solve(self, X, B):
         """X: initial guess in / solution out; B: right-hand sides.  Returns a dict."""
         r = GmresResult()
-        rc = solver_lib().b200_belos_solve(self.SOLVER, self.op._h, X._h, B._h, C.byref(self.params), C.byref(r))
+        rc = solver_lib().b200_belos_solve_prec(self.SOLVER, self.op._h, self.prec._h if self.prec is not None else None,
+                                                self.left, X._h, B._h, C.byref(self.params), C.byref(r))
         check(rc)
         self.result = dict(converged=bool(r.converged), num_iters=r.num_iters, achieved_tol=r.achieved_tol,
                            loss_of_accuracy=bool(r.loss_of_accuracy), solve_seconds=r.solve_seconds,
