@@ -67,6 +67,27 @@ def main():
         assert abs(r["num_iters"] - g["num_iters"]) <= max(1, round(0.02 * g["num_iters"])), (label, r["num_iters"], g["num_iters"])
         assert np.abs(X.to_numpy() - Xe.to_numpy()).max() <= 10 * max(g["max_abs_err"], 1e-12)
         out[label] = dict(iters=r["num_iters"], golden=g["num_iters"])
+    # other solver managers and the Chebyshev right preconditioner on the distributed path
+    more = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_solves_managers.json")))
+    more.update(json.load(open(os.path.join(ROOT, "tests", "golden", "ref_solves_prec.json"))))
+    for label, g in sorted(more.items()):
+        name, dims, b = g["matrix"], tuple(g["dims"]), g["block_size"]
+        op, n, lo, hi = tb.dist.local_operator(ctx, name, dims)
+        ctx.set_seed(1)
+        Xe = tb.dist.local_multivec(ctx, n, lo, hi, b, zero=False)
+        Xe.MvRandom()
+        B = tb.dist.local_multivec(ctx, n, lo, hi, b)
+        op.Apply(Xe, B)
+        X = tb.dist.local_multivec(ctx, n, lo, hi, b)
+        ch = g.get("cheby")
+        P = tb.Chebyshev(op, degree=ch["degree"], lambda_max=ch.get("lambda_max", -1.0), seed=1) if ch else None
+        mgr = tb.SOLVER_MANAGERS[g["solver"]](op, block_size=b, num_blocks=g["num_blocks"], max_iters=g.get("max_iters", -1),
+                                              max_restarts=g["max_restarts"], tol=g["tol"], ortho=g["ortho"], right_prec=P)
+        r = mgr.solve(X, B)
+        assert r["converged"], (label, r)
+        assert max(r["true_rel_resid"]) <= g["tol"] * 1.001, (label, r)
+        assert abs(r["num_iters"] - g["num_iters"]) <= max(1, round(0.02 * g["num_iters"])), (label, r["num_iters"], g["num_iters"])
+        out[label] = dict(iters=r["num_iters"], golden=g["num_iters"])
     ctx.sync()
     if rank == 0:
         print("NCCL_WORKER_OK " + json.dumps(dict(world=world, results=out)))
