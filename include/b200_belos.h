@@ -193,6 +193,22 @@ int b200_galeri_generate(const char* name, int nx, int ny, int nz, double conv, 
                          int64_t row_begin, int64_t row_end, int64_t* nnz, int32_t* rowptr,
                          int64_t* colind_global, double* values);
 
+/* ---- matrix ingest ------------------------------------------------
+ * Harwell-Boeing file -> the rows [row_begin, row_end) (row_end < 0: all) of the matrix the reference
+ * builds from it: Belos::Util::createEpetraProblem (belos/epetra/src/BelosEpetraUtils.cpp:81-200)
+ * over Trilinos_Util_read_hb (triutils/src/Trilinos_Util_read_hb.cpp:49-230) -- real assembled square
+ * matrices, symmetric storage mirrored, an explicit diagonal entry in every row (MSR), columns
+ * sorted.  rhs / xexact (length row_end - row_begin) are filled when the file carries a full
+ * right-hand side with an exact solution (*has_rhs = 1).  Two-call protocol: rowptr == NULL -> only
+ * *n, *nnz, *has_rhs are set.  Output is what b200_op_create_csr takes. */
+int b200_read_hb(const char* path, int64_t row_begin, int64_t row_end, int64_t* n, int64_t* nnz,
+                 int32_t* rowptr, int64_t* colind_global, double* values, double* rhs, double* xexact,
+                 int* has_rhs);
+/* MatrixMarket "matrix coordinate real general|symmetric" (triutils/src/
+ * Trilinos_Util_ReadMatrixMarket2Epetra.cpp): repeated entries are summed, no diagonal is added. */
+int b200_read_matrix_market(const char* path, int64_t row_begin, int64_t row_end, int64_t* n,
+                            int64_t* nnz, int32_t* rowptr, int64_t* colind_global, double* values);
+
 /* ---- right preconditioning through the same boundary -------------
  * Element-wise product with a broadcast vector: mv(:,j) = scalar_this*mv(:,j) + scalar_ab * A(:,0) .* B(:,j)
  * Epetra_MultiVector::Multiply(double ScalarAB, A, B, double ScalarThis) with a single-vector A

@@ -155,6 +155,47 @@ def gen_cheby():
     json.dump(res, open(path, "w"), indent=1, sort_keys=True)
 
 
+# matrix ingest: generated files, read by the reference's own readers
+INGEST = [  # (file, kind, matrix, dims, symmetric, with rhs)
+    ("ingest_recirc2d_12x9.hb", "hb", "Recirc2D", (12, 9, 1), False, True),
+    ("ingest_laplace2d_10x8_rsa.hb", "hb", "Laplace2D", (10, 8, 1), True, False),
+    ("ingest_laplace3d_7x6x5.mtx", "mm", "Laplace3D", (7, 6, 5), False, False),
+    ("ingest_laplace2d_10x8_sym.mtx", "mm", "Laplace2D", (10, 8, 1), True, False),
+]
+
+
+def gen_ingest():
+    from oracle import hb_write
+    out, solves = {}, {}
+    for fn, kind, name, dims, sym, with_rhs in INGEST:
+        kw = dict(conv=1.0, diff=1e-5) if name == "Recirc2D" else {}
+        n, rp, ci, va = matrix(name, dims, **kw)
+        path = os.path.join(OUT, fn)
+        if kind == "hb":
+            xe = b = None
+            if with_rhs:
+                xe, _ = ref.random(3, n, 1)
+                b = ref.apply(rp, ci, va, xe)[:, 0]
+                xe = xe[:, 0]
+            hb_write.write_hb(path, n, rp, ci, va, symmetric=sym, rhs=b, xexact=xe)
+        else:
+            hb_write.write_mm(path, n, rp, ci, va, symmetric=sym)
+        n2, rp2, ci2, va2, b2, x2 = ref.read_matrix(path, kind)         # the reference's reader
+        assert n2 == n
+        out[fn + "_rowptr"], out[fn + "_colind"], out[fn + "_values"] = rp2, ci2, va2
+        if with_rhs:
+            out[fn + "_b"], out[fn + "_xexact"] = b2, x2
+        # bl_gmres_hb-style solve on the matrix as read (belos/epetra/test/BlockGmres/test_bl_gmres_hb.cpp)
+        xs, _ = ref.random(1, n, 2)
+        B = ref.apply(rp2, ci2, va2, xs)
+        X, r = ref.block_gmres(rp2, ci2, va2, B, block_size=2, num_blocks=60, max_iters=200, max_restarts=100, tol=1e-6)
+        r.update(file=fn, kind=kind, block_size=2, num_blocks=60, max_iters=200, max_restarts=100, tol=1e-6, ortho="DGKS")
+        solves[fn] = r
+        print(fn, n, len(va2), r["num_iters"], r["converged"], flush=True)
+    np.savez_compressed(os.path.join(OUT, "ref_ingest.npz"), **out)
+    json.dump(solves, open(os.path.join(OUT, "ref_solves_ingest.json"), "w"), indent=1, sort_keys=True)
+
+
 def gen_solves(cases, fn, threads=1):
     path = os.path.join(OUT, fn)
     res = json.load(open(path)) if os.path.exists(path) else {}
@@ -180,7 +221,9 @@ def gen_solves(cases, fn, threads=1):
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    if "--cheby" in sys.argv:
+    if "--ingest" in sys.argv:
+        gen_ingest()
+    elif "--cheby" in sys.argv:
         gen_cheby()
     elif "--managers" in sys.argv:
         gen_solves(SOLVES_MANAGERS, "ref_solves_managers.json")

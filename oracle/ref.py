@@ -209,6 +209,23 @@ def belos_solve_cheby(rowptr, colind, values, B, cheby, X0=None, block_size=1, n
                    true_rel_resid=[r.true_rel_resid[i] for i in range(min(k, 64))])
 
 
+def read_matrix(path, kind="hb"):
+    """The reference's own reader: kind "hb" = Trilinos_Util_read_hb + the row insertion of
+    Belos::Util::createEpetraProblem; kind "mm" = Trilinos_Util_ReadMatrixMarket2Epetra.
+    Returns (n, rowptr, colind, values, b, xexact) (b, xexact only for "hb")."""
+    k = 0 if kind == "hb" else 1
+    n, nnz = C.c_int64(), C.c_int64()
+    pth = os.fsencode(path)
+    _ck(lib().ref_read_matrix(k, pth, C.byref(n), C.byref(nnz), None, None, None, None, None))
+    rp = np.zeros(n.value + 1, dtype=np.int32)
+    ci = np.zeros(max(nnz.value, 1), dtype=np.int32)
+    va = np.zeros(max(nnz.value, 1))
+    b = np.zeros(max(n.value, 1))
+    xe = np.zeros(max(n.value, 1))
+    _ck(lib().ref_read_matrix(k, pth, C.byref(n), C.byref(nnz), _i32(rp), _i32(ci), _d(va), _d(b), _d(xe)))
+    return n.value, rp, ci[:nnz.value], va[:nnz.value], b[:n.value], xe[:n.value]
+
+
 def timer_summary():
     buf = C.create_string_buffer(1 << 16)
     lib().ref_timer_summary(buf, len(buf))

@@ -35,6 +35,8 @@
 #include "Galeri_CrsMatrices.h"
 #include "Galeri_Maps.h"
 #include "Ifpack_Chebyshev.h"
+#include "Trilinos_Util.h"
+#include "Trilinos_Util_ReadMatrixMarket2Epetra.h"
 #include "Teuchos_ParameterList.hpp"
 #include "Teuchos_RCP.hpp"
 #include "Teuchos_SerialDenseMatrix.hpp"
@@ -417,6 +419,79 @@ extern "C" int ref_belos_solve_cheby_csr(const char* solver_name, int64_t n, con
   const int rc = ref_belos_solve_csr(solver_name, n, rowptr, colind, values, numrhs, Bh, ldb, Xh, ldx, p, r);
   g_cheby = nullptr;
   return rc;
+}
+
+// ---- matrix ingest oracle: the reference's own readers.
+// kind 0: Harwell-Boeing through Trilinos_Util_read_hb + the row insertion of
+//         Belos::Util::createEpetraProblem (belos/epetra/src/BelosEpetraUtils.cpp:110-170, serial);
+// kind 1: MatrixMarket through Trilinos_Util_ReadMatrixMarket2Epetra.
+// Two-call protocol (rowptr == NULL: sizes only); the matrix is kept between the two calls.
+namespace {
+RCP<Epetra_CrsMatrix> g_read;
+std::vector<double> g_read_b, g_read_x;
+std::string g_read_key;
+}  // namespace
+
+extern "C" int ref_read_matrix(int kind, const char* path, int64_t* n, int64_t* nnz, int32_t* rowptr,
+                               int32_t* colind, double* values, double* b, double* xexact) {
+  try {
+    static Epetra_SerialComm comm;
+    const std::string key = std::to_string(kind) + ":" + path;
+    if (key != g_read_key) {
+      g_read = Teuchos::null;
+      if (kind == 0) {
+        int N = 0, nz = 0, *bindx = 0;
+        double *val = 0, *xg = 0, *bb = 0, *xe = 0;
+        Trilinos_Util_read_hb(const_cast<char*>(path), 0, &N, &nz, &val, &bindx, &xg, &bb, &xe);
+        Epetra_Map map(N, 0, comm);
+        std::vector<int> numnz(N);
+        for (int i = 0; i < N; ++i) numnz[i] = bindx[i + 1] - bindx[i] + 1;
+        g_read = rcp(new Epetra_CrsMatrix(Copy, map, numnz.data()));
+        for (int i = 0; i < N; ++i) {
+          g_read->InsertGlobalValues(i, bindx[i + 1] - bindx[i], val + bindx[i], bindx + bindx[i]);
+          g_read->InsertGlobalValues(i, 1, val + i, &i);
+        }
+        g_read->FillComplete();
+        g_read->OptimizeStorage();
+        g_read_b.assign(bb, bb + N);
+        g_read_x.assign(xe, xe + N);
+        free(val); free(bindx); free(xg); free(bb); free(xe);
+      } else {
+        Epetra_Map* map = 0;
+        Epetra_CrsMatrix* A = 0;
+        Epetra_Vector *x = 0, *bv = 0, *xe = 0;
+        if (Trilinos_Util_ReadMatrixMarket2Epetra(const_cast<char*>(path), comm, map, A, x, bv, xe) != 0)
+          throw std::runtime_error("Trilinos_Util_ReadMatrixMarket2Epetra failed");
+        A->OptimizeStorage();
+        g_read = rcp(A);
+        g_read_b.clear();
+        g_read_x.clear();
+        delete x; delete bv; delete xe;   // (the map must outlive the matrix: leaked on purpose)
+      }
+      g_read_key = key;
+    }
+    const int N = g_read->NumMyRows();
+    *n = N;
+    *nnz = g_read->NumMyNonzeros();
+    if (!rowptr) return 0;
+    int pos = 0;
+    for (int i = 0; i < N; ++i) {
+      int cnt = 0, *idx = 0;
+      double* v = 0;
+      g_read->ExtractMyRowView(i, cnt, v, idx);
+      rowptr[i] = pos;
+      for (int k = 0; k < cnt; ++k) {
+        colind[pos] = g_read->GCID(idx[k]);
+        values[pos++] = v[k];
+      }
+    }
+    rowptr[N] = pos;
+    if (b && !g_read_b.empty()) std::copy(g_read_b.begin(), g_read_b.end(), b);
+    if (xexact && !g_read_x.empty()) std::copy(g_read_x.begin(), g_read_x.end(), xexact);
+    return 0;
+  } catch (const std::exception& e) {
+    return fail(e);
+  }
 }
 
 extern "C" int ref_timer_summary(char* buf, int buflen) {

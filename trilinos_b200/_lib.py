@@ -79,6 +79,9 @@ _SIGS = {
     "b200_op_destroy": (C.c_int, [vp]),
     "b200_op_apply": (C.c_int, [vp, vp, vp, C.c_int]),
     "b200_op_info": (C.c_int, [vp, P(c_i64), P(c_i64), P(c_i64), P(c_i64), P(c_i64)]),
+    "b200_read_hb": (C.c_int, [C.c_char_p, c_i64, c_i64, P(c_i64), P(c_i64), P(c_i32), P(c_i64), P(c_dbl), P(c_dbl),
+                               P(c_dbl), P(C.c_int)]),
+    "b200_read_matrix_market": (C.c_int, [C.c_char_p, c_i64, c_i64, P(c_i64), P(c_i64), P(c_i32), P(c_i64), P(c_dbl)]),
     "b200_mv_multiply_elementwise": (C.c_int, [vp, c_dbl, vp, vp, c_dbl]),
     "b200_op_extract_diagonal": (C.c_int, [vp, P(vp)]),
     "b200_cheby_default_params": (None, [vp]),

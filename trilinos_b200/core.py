@@ -7,6 +7,7 @@ parity tests read like the reference's own MVOPTester.  numpy is used only to ho
 buffers; all arithmetic on n-sized data happens on the GPU.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -328,6 +329,39 @@ def build_colmap(n_global, nranks, rank, colind_global):
     if ng < 0:
         raise B200Error(-1, lib.b200_last_error().decode())
     return loc[:nnz], gids[:ng], own[:ng]
+
+
+def read_hb(path, row_begin=0, row_end=-1):
+    """Harwell-Boeing file -> (n, rowptr, colind_global, values, rhs or None, xexact or None) for rows
+    [row_begin, row_end): the matrix Belos::Util::createEpetraProblem builds (b200_read_hb)."""
+    n, nnz, has = c_i64(), c_i64(), C.c_int()
+    pth = os.fsencode(path)
+    check(lib.b200_read_hb(pth, row_begin, row_end, C.byref(n), C.byref(nnz), None, None, None, None, None, C.byref(has)))
+    re_ = n.value if row_end < 0 else row_end
+    nl = re_ - row_begin
+    rp = np.zeros(nl + 1, dtype=np.int32)
+    ci = np.zeros(max(nnz.value, 1), dtype=np.int64)
+    va = np.zeros(max(nnz.value, 1), dtype=np.float64)
+    rhs = np.zeros(max(nl, 1)) if has.value else None
+    xe = np.zeros(max(nl, 1)) if has.value else None
+    check(lib.b200_read_hb(pth, row_begin, row_end, C.byref(n), C.byref(nnz), rp.ctypes.data_as(P(c_i32)),
+                           ci.ctypes.data_as(P(c_i64)), _dptr(va), _dptr(rhs) if has.value else None,
+                           _dptr(xe) if has.value else None, C.byref(has)))
+    return (n.value, rp, ci[:nnz.value], va[:nnz.value], rhs[:nl] if has.value else None, xe[:nl] if has.value else None)
+
+
+def read_matrix_market(path, row_begin=0, row_end=-1):
+    """MatrixMarket coordinate real general|symmetric -> (n, rowptr, colind_global, values) (b200_read_matrix_market)."""
+    n, nnz = c_i64(), c_i64()
+    pth = os.fsencode(path)
+    check(lib.b200_read_matrix_market(pth, row_begin, row_end, C.byref(n), C.byref(nnz), None, None, None))
+    re_ = n.value if row_end < 0 else row_end
+    rp = np.zeros(re_ - row_begin + 1, dtype=np.int32)
+    ci = np.zeros(max(nnz.value, 1), dtype=np.int64)
+    va = np.zeros(max(nnz.value, 1), dtype=np.float64)
+    check(lib.b200_read_matrix_market(pth, row_begin, row_end, C.byref(n), C.byref(nnz), rp.ctypes.data_as(P(c_i32)),
+                                      ci.ctypes.data_as(P(c_i64)), _dptr(va)))
+    return n.value, rp, ci[:nnz.value], va[:nnz.value]
 
 
 def galeri(name, nx, ny=1, nz=1, conv=1.0, diff=1.0e-5, row_begin=0, row_end=None):
