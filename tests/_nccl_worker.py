@@ -38,8 +38,12 @@ def main():
         X.MvRandom()                                   # partition-independent: must equal rows [lo,hi) of xg
         assert np.array_equal(X.to_numpy(), xg[lo:hi]), f"{name}: MvRandom is not partition independent"
         Y = tb.dist.local_multivec(ctx, n, lo, hi, k)
-        op.Apply(X, Y)
         yg = oracle.spmm(rp, ci.astype(np.int32), va, xg)
+        # one column first: the halo window is then re-made (collectively) for the wider block below
+        op.Apply(X.CloneView([k - 1]), Y.CloneViewNonConst([0]))
+        assert rel(Y.to_numpy()[:, 0], yg[lo:hi, k - 1]) <= TOL, f"{name}: single-column apply"
+        op.Apply(X, Y)
+        op.Apply(X, Y)                                  # back-to-back applies: ghost-block parity alternates
         e_apply = rel(Y.to_numpy(), yg[lo:hi])
         e_gram = rel(Y.MvTransMv(1.0, X), oracle.trans_mv(1.0, xg, yg))
         e_dot = rel(Y.MvDot(X), oracle.dot(yg, xg))
