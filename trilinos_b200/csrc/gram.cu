@@ -31,6 +31,8 @@
 #include "device_utils.cuh"
 #include "runtime.cuh"
 
+#include <cstdlib>
+
 namespace b200 {
 
 namespace {
@@ -69,6 +71,7 @@ struct GramArgs {
   int64_t lda, ldv, n;
   int p, q;          // columns of A, columns of V handled by this launch (q <= Q)
   int sub;           // 64-row substeps per tile (tile rows R = 64*sub)
+  int rows;          // DMMA kernel: rows per tile (R = 4 mod 16: conflict-free fragment loads)
   int nstage;
   int wc_log2;       // consumer warps = WC column groups x WR row groups
   int64_t ntiles;    // ceil(n / R)
@@ -218,6 +221,176 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1)
   publish_flag(g.flag, g.seq);
 }
 
+// ---------------------------------------------------------------------------------------------
+// FP64 tensor-core (DMMA) variant for q = 8 / 16 right-hand sides.
+//
+// At q = 16 the Gram needs 2 q / 8 = 4 flop per streamed byte, i.e. ~26 TFLOP/s to stay on the HBM
+// roofline -- 70 % of the FP64 peak (37 TFLOP/s, profiles/r1_dmma_probe_s30.txt).  The SIMT kernel
+// above re-reads the V tile from shared memory for every 4 columns of A (20 LDS.128 per 128 DFMA)
+// and is bound by the shared-memory pipe (34-53 % of HBM peak).  mma.sync.m8n8k4.f64 computes an
+// 8 x 8 block of A^T V over 4 rows per instruction with ONE 8-byte operand per lane for A and for
+// V: the same FP64 peak at 1/8 of the issue slots and ~1/10 of the shared-memory traffic.
+//
+// Row-tile-major: for each R-row tile the V tile is staged ONCE (its own double buffer) and the
+// 32-column blocks of A stream through the stage ring against it -- a DMMA accumulator is 2
+// doubles per 8 x 8 block, so a warp keeps the accumulators of all (up to 8) column blocks of a
+// pass in registers (12 consumer warps + the producer = 13 warps, at most 4 per SM sub-partition,
+// so each thread may use 128 registers).  Shared-memory fill traffic == algorithmic bytes, and the TMA rows stay long
+// (R * 8 >= 1 KB).  12 consumer warps = 4 column tiles (8 columns of A) x 3 row groups; fragment
+// lane l = (row 4 step + l%4, column 8 tile + l/4); R = 4 (mod 16) makes the column stride 8 banks
+// (mod 32): every fragment load is two conflict-free wavefronts.
+constexpr int kMaxCB = 8;   // 32-column blocks per pass (256 columns)
+
+template <int NTQ>  // q == 8 * NTQ
+__global__ void __launch_bounds__(13 * 32, 1)
+    gram_dmma_kernel(const GramArgs g, const __grid_constant__ CUtensorMap tmA,
+                     const __grid_constant__ CUtensorMap tmV) {
+  constexpr int NW = 12, NT = (NW + 1) * 32, Q = 8 * NTQ;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint64_t full_bar[kMaxStages], empty_bar[kMaxStages], fullv_bar[kMaxStages],
+      emptyv_bar[kMaxStages];
+  __shared__ double red[4 * kTC * Q];  // [row group][column of the block][rhs]
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int R = g.rows;
+  const int ncb = (g.p + kTC - 1) / kTC;
+  const int npass = (ncb + kMaxCB - 1) / kMaxCB;
+  const int wfull = min((g.p + 7) / 8 * 8, kTC);
+  const uint32_t a_bytes = (uint32_t)(wfull * R) * 8u, v_bytes = (uint32_t)(Q * R) * 8u;
+  unsigned char* vbuf0 = reinterpret_cast<unsigned char*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  const int nv = g.sub;  // V buffers: 2 when several column blocks share a tile, else ring depth
+  unsigned char* stage0 = vbuf0 + (size_t)nv * v_bytes;
+  const int64_t t_begin = g.ntiles * blockIdx.x / gridDim.x;
+  const int64_t t_end = g.ntiles * (blockIdx.x + 1) / gridDim.x;
+  const int ntile_cta = (int)(t_end - t_begin);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < g.nstage; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], NW);
+    }
+    for (int s = 0; s < nv; ++s) {
+      mbar_init(&fullv_bar[s], 1);
+      mbar_init(&emptyv_bar[s], NW);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  if (warp == NW) {
+    if (lane == 0) {
+      int s = 0, vb = 0;
+      uint32_t ph = 0, vph = 0;
+      const uint64_t pol_a = l2_policy_evict_first();
+      const uint64_t pol_v = l2_policy_evict_last();
+      for (int ps = 0; ps < npass; ++ps) {
+        const int cb0 = ps * kMaxCB, cb1 = min(ncb, cb0 + kMaxCB);
+        for (int t = 0; t < ntile_cta; ++t) {
+          const int r0 = (int)((t_begin + t) * R);
+          mbar_wait(&emptyv_bar[vb], vph ^ 1u);
+          mbar_expect_tx(&fullv_bar[vb], v_bytes);
+          tma_load_2d(vbuf0 + (size_t)vb * v_bytes, &tmV, r0, 0, &fullv_bar[vb], pol_v);
+          if (++vb == nv) { vb = 0; vph ^= 1u; }
+          for (int cb = cb0; cb < cb1; ++cb) {
+            mbar_wait(&empty_bar[s], ph ^ 1u);
+            mbar_expect_tx(&full_bar[s], a_bytes);
+            tma_load_2d(stage0 + (size_t)s * a_bytes, &tmA, r0, cb * kTC, &full_bar[s], pol_a);
+            if (++s == g.nstage) { s = 0; ph ^= 1u; }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // wfull / 8 column tiles x NW / (wfull / 8) row groups (4 x 3 for a full block)
+    const int nmt = wfull >> 3, nrg = NW / nmt;
+    const int mt = warp % nmt, rg = warp / nmt;
+    const uint32_t colstride = (uint32_t)R * 8u;
+    const uint32_t frag = (uint32_t)(lane >> 2) * colstride + (uint32_t)(lane & 3) * 8u;
+    const uint32_t a_off = smem_u32(stage0) + (uint32_t)(8 * mt) * colstride + frag;
+    const uint32_t v_off = smem_u32(vbuf0) + frag;
+    const int nsteps = R >> 2;
+    int s = 0, vb = 0;
+    uint32_t ph = 0, vph = 0;
+    for (int ps = 0; ps < npass; ++ps) {
+      const int cb0 = ps * kMaxCB;
+      const int ncbp = min(ncb - cb0, kMaxCB);
+      double c[kMaxCB][NTQ][2];
+#pragma unroll
+      for (int i = 0; i < kMaxCB; ++i)
+#pragma unroll
+        for (int nt = 0; nt < NTQ; ++nt) c[i][nt][0] = c[i][nt][1] = 0.0;
+      for (int t = 0; t < ntile_cta; ++t) {
+        mbar_wait(&fullv_bar[vb], vph);
+        const uint32_t vst = v_off + (uint32_t)vb * v_bytes;
+#pragma unroll
+        for (int i = 0; i < kMaxCB; ++i) {
+          if (i < ncbp) {
+            mbar_wait(&full_bar[s], ph);
+            // columns >= p of the last block are zero-filled by the TMA unit
+            if (rg < nrg && 8 * mt < min(kTC, g.p - (cb0 + i) * kTC)) {
+              const uint32_t ast = a_off + (uint32_t)s * a_bytes;
+              for (int step = rg; step < nsteps; step += nrg) {
+                const uint32_t row = (uint32_t)step * 32u;  // 4 rows x 8 bytes
+                const double a = lds_f64(ast + row);
+#pragma unroll
+                for (int nt = 0; nt < NTQ; ++nt) {
+                  const double b = lds_f64(vst + (uint32_t)(8 * nt) * colstride + row);
+                  asm volatile(
+                      "mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                      : "+d"(c[i][nt][0]), "+d"(c[i][nt][1])
+                      : "d"(a), "d"(b));
+                }
+              }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[s]);
+            if (++s == g.nstage) { s = 0; ph ^= 1u; }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&emptyv_bar[vb]);
+        if (++vb == nv) { vb = 0; vph ^= 1u; }
+      }
+      // C fragment: lane l holds C(m = l/4, n = 8 nt + 2 (l%4) + {0,1}); the 4 row groups of a
+      // column tile are summed through shared memory, block by block
+#pragma unroll
+      for (int i = 0; i < kMaxCB; ++i) {
+        if (i < ncbp) {
+          const int col0 = (cb0 + i) * kTC;
+          const int wdt = min(kTC, g.p - col0);
+          if (rg < nrg) {
+            double* r = red + ((size_t)rg * wfull + 8 * mt + (lane >> 2)) * Q + 2 * (lane & 3);
+#pragma unroll
+            for (int nt = 0; nt < NTQ; ++nt) {
+              r[8 * nt] = c[i][nt][0];
+              r[8 * nt + 1] = c[i][nt][1];
+            }
+          }
+          consumer_bar<NW * 32>();
+          for (int e = threadIdx.x; e < wdt * Q; e += NW * 32) {
+            const int cc = e / Q, k = e % Q;
+            double sres = 0.0;
+            for (int r = 0; r < nrg; ++r) sres += red[((size_t)r * wfull + cc) * Q + k];
+            g.ws[(size_t)blockIdx.x * (size_t)(g.p * g.q) + (size_t)k * g.p + col0 + cc] = sres;
+          }
+          consumer_bar<NW * 32>();
+        }
+      }
+    }
+  }
+
+  const int nent = g.p * g.q;
+  const bool fin = fold_partials_tall<NT>(g.ws, g.ticket, nent, (int)gridDim.x, (int)blockIdx.x,
+                                          [&](int e, double sres) {
+                                            const int k = e / g.p, col = e % g.p;
+                                            g.out[(size_t)k * g.ldc + col] = g.alpha * sres;
+                                          });
+  if (!fin) return;
+  publish_flag(g.flag, g.seq);
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -293,6 +466,51 @@ int launch_gram_t(Ctx* ctx, const double* A, int64_t lda, int p, const double* V
   return 0;
 }
 
+template <int NTQ>
+int launch_gram_dmma(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, int64_t ldv,
+                     int64_t n, double alpha, double* out, int ldc, uint64_t* flag) {
+  constexpr int Q = 8 * NTQ;
+  GramArgs g;
+  g.A = A; g.V = V; g.lda = lda; g.ldv = ldv; g.n = n; g.p = p; g.q = Q;
+  const int wfull = std::min((p + 7) / 8 * 8, kTC);
+  // rows per tile: R = 4 (mod 16).  One column block: V and A tiles travel together, >= 4 deep.
+  // Several column blocks: two V buffers (a V tile lives for ncb stages) + >= 4 A stages.
+  const bool single = p <= kTC;
+  int R = (int)(kSmemBudget / ((size_t)(single ? 4 * (wfull + Q) : 4 * wfull + 2 * Q) * sizeof(double)));
+  R = std::min(R, 244);
+  R = (R - 4) / 16 * 16 + 4;
+  g.rows = R;
+  g.wc_log2 = 0;
+  const size_t a_bytes = (size_t)wfull * R * sizeof(double), v_bytes = (size_t)Q * R * sizeof(double);
+  if (single) {
+    g.nstage = (int)std::min<size_t>(kMaxStages, kSmemBudget / (a_bytes + v_bytes));
+    g.sub = g.nstage;
+  } else {
+    g.sub = 2;
+    g.nstage = (int)std::min<size_t>(kMaxStages, (kSmemBudget - 2 * v_bytes) / a_bytes);
+  }
+  g.ntiles = (n + R - 1) / R;
+  g.alpha = alpha;
+  g.ws = ctx->ws; g.ticket = ctx->ticket; g.out = out; g.ldc = ldc; g.flag = flag; g.seq = ctx->seq;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->num_sms, g.ntiles));
+  if ((size_t)p * Q * (grid + grid / 16 + 1) * sizeof(double) > kWorkspaceBytes)
+    return fail(B200_ERR_ARG, "MvTransMv: partial-sum workspace too small");
+  CUtensorMap tmA, tmV;
+  B200_TRY(make_tmap(&tmA, A, n, p, lda, R, wfull));
+  B200_TRY(make_tmap(&tmV, V, n, Q, ldv, R, Q));
+  const size_t smem = (size_t)g.sub * v_bytes + a_bytes * g.nstage + 128;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(gram_dmma_kernel<NTQ>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(208u << 10)));
+    attr_set = true;
+  }
+  gram_dmma_kernel<NTQ><<<grid, 13 * 32, smem, ctx->stream>>>(g, tmA, tmV);
+  ++ctx->launches;
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace
 
 int launch_gram(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, int64_t ldv, int q,
@@ -309,7 +527,15 @@ int launch_gram(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, 
     const double* Vk = V + (size_t)k0 * ldv;
     double* outk = out + (size_t)k0 * ldc;
     uint64_t* flag = (last && k0 + step >= q) ? ctx->result_flag() : nullptr;
-    if (step > 8)
+    static const bool dmma_on = [] {
+      const char* e = getenv("B200_GRAM_DMMA");
+      return !(e && e[0] == '0');
+    }();
+    if (step == 16 && dmma_on)
+      rc = launch_gram_dmma<2>(ctx, A, lda, p, Vk, ldv, n, alpha, outk, ldc, flag);
+    else if (step == 8 && dmma_on)
+      rc = launch_gram_dmma<1>(ctx, A, lda, p, Vk, ldv, n, alpha, outk, ldc, flag);
+    else if (step > 8)
       rc = launch_gram_t<16, 4, 8>(ctx, A, lda, p, Vk, ldv, step, n, alpha, outk, ldc, flag);
     else if (step > 4)
       rc = launch_gram_t<8, 4, 8>(ctx, A, lda, p, Vk, ldv, step, n, alpha, outk, ldc, flag);
