@@ -41,30 +41,11 @@ constexpr int kMaxStages = 8;
 constexpr size_t kSmemBudget = 200u << 10;
 constexpr int kTC = 32;  // columns of A per column block
 
-// 2-D TMA tensor copy global -> shared (coordinates: c0 = row, c1 = column), completion on an
-// mbarrier (SASS: UTMALDG)
-// `policy`: L2 eviction policy (createpolicy).  The basis A is touched once per call -> evict_first;
-// the block V is re-read once per 32-column block of A -> evict_last.  Without the hints the A
-// stream pushed V out of L2 and V came back from DRAM every column block (ncu: 924 MB read for
-// 832 algorithmic MB at p = 100, q = 4).
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* tmap, int c0, int c1,
-                                            uint64_t* bar, uint64_t policy) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3}], [%4], %5;" ::
-          "r"(smem_u32(dst)),
-      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(c0), "r"(c1), "r"(smem_u32(bar)), "l"(policy)
-      : "memory");
-}
 __device__ __forceinline__ double2 lds128(uint32_t addr) {
   double2 v;
   asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
   return v;
 }
-template <int NTHREADS>
-__device__ __forceinline__ void consumer_bar() {
-  asm volatile("bar.sync 1, %0;" ::"n"(NTHREADS) : "memory");
-}
-
 struct GramArgs {
   const double* A;
   const double* V;
@@ -391,12 +372,14 @@ __global__ void __launch_bounds__(13 * 32, 1)
   publish_flag(g.flag, g.seq);
 }
 
+}  // namespace
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-EncodeTiledFn encode_tiled_fn() {
+static EncodeTiledFn encode_tiled_fn() {
   static EncodeTiledFn fn = nullptr;
   if (!fn) {
     void* p = nullptr;
@@ -427,6 +410,8 @@ int make_tmap(CUtensorMap* tm, const double* base, int64_t n, int ncols, int64_t
     return failf(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return 0;
 }
+
+namespace {
 
 template <int Q, int CPW, int NW>
 int launch_gram_t(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, int64_t ldv, int q,

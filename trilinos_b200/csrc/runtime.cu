@@ -302,6 +302,7 @@ extern "C" int b200_ctx_create(int device, b200_ctx** out) {
   B200_CUDA(cudaMalloc((void**)&c->red_d, kMailboxDoubles * sizeof(double)));
   B200_CUDA(cudaMalloc((void**)&c->aux_d, (size_t)kAuxSlots * kAuxSlotDoubles * sizeof(double)));
   B200_CUDA(cudaMalloc((void**)&c->dB, kStageSlotBytes));
+  B200_CUDA(cudaMalloc((void**)&c->dBpack, kPackBytes));
   B200_CUDA(cudaHostAlloc((void**)&c->stage_h, kStageSlots * kStageSlotBytes, cudaHostAllocDefault));
   for (int i = 0; i < kStageSlots; ++i)
     B200_CUDA(cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming));
@@ -330,6 +331,7 @@ extern "C" int b200_ctx_destroy(b200_ctx* c) {
   cudaFree(c->red_d);
   cudaFree(c->aux_d);
   cudaFree(c->dB);
+  cudaFree(c->dBpack);
   if (c->flush_buf) cudaFree(c->flush_buf);
   cudaEventDestroy(c->ev_comm);
   cudaEventDestroy(c->ev_compute);

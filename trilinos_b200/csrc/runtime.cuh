@@ -30,6 +30,7 @@ constexpr int kAuxSlots = 32;                   // mailbox slots for results of 
 constexpr int kAuxSlotDoubles = 64;             // <= 32 columns x {self, with-old}
 constexpr size_t kAuxBase = kMailboxDoubles - (size_t)kAuxSlots * kAuxSlotDoubles;
 constexpr size_t kStageSlotBytes = 512u << 10; // host B blocks for MvTimesMatAddMv
+constexpr size_t kPackBytes = 1u << 20;        // the same block in DMMA fragment order (16 -> 24 columns)
 
 #define B200_CUDA(call)                                                                   \
   do {                                                                                    \
@@ -90,6 +91,7 @@ struct Ctx {
   double* red_d = nullptr;         // device-side result (multi-rank: allreduce in place)
   double* aux_d = nullptr;         // multi-rank: per-rank partials of fused epilogues (kAuxSlots slots)
   double* dB = nullptr;            // device copy of the host dense block B
+  double* dBpack = nullptr;        // B re-laid in DMMA fragment order (update.cu)
   char* stage_h = nullptr;         // pinned staging ring for B
   cudaEvent_t stage_ev[kStageSlots] = {};
   bool stage_used[kStageSlots] = {};
