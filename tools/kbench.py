@@ -41,6 +41,8 @@ x1 = X.CloneView([0])
 for p in (1, 3):
     Qp = Q.CloneView(list(range(p)))
     timed(f"trans_mv p={p} q=1 (L2)", lambda: x1.MvTransMv(1.0, Qp), flush=False)
+    Bs = np.random.default_rng(0).uniform(-1, 1, (p, 1)) * 1e-3
+    timed(f"times_mat_add_mv p={p} q=1 (L2)", lambda: x1.MvTimesMatAddMv(-1.0, Qp, Bs, 1.0), flush=False)
 timed(f"dot k={b} (L2)", lambda: X.MvDot(X), flush=False)
 timed(f"dot k=1 (L2)", lambda: x1.MvDot(x1), flush=False)
 timed(f"norm k={b} (L2)", lambda: X.MvNorm(), flush=False)
@@ -54,6 +56,18 @@ t0 = time.perf_counter()
 for _ in range(200): x1.MvDot(x1)
 t1 = time.perf_counter()
 print(f"dot k=1 round trip: {(t1-t0)/200*1e6:.1f} us")
+for p in (4, 32):
+    Qp = Q.CloneView(list(range(p)))
+    X.MvTransMv(1.0, Qp); ctx.sync()
+    t0 = time.perf_counter()
+    for _ in range(200): X.MvTransMv(1.0, Qp)
+    t1 = time.perf_counter()
+    print(f"trans_mv p={p} q={b} host round trip (L2 warm): {(t1-t0)/200*1e6:.1f} us")
+Q3 = Q.CloneView([0, 1, 2])
+t0 = time.perf_counter()
+for _ in range(200): x1.MvTransMv(1.0, Q3)
+t1 = time.perf_counter()
+print(f"trans_mv p=3 q=1 host round trip: {(t1-t0)/200*1e6:.1f} us")
 t0 = time.perf_counter()
 for _ in range(200): X.MvScale(1.0000001)
 ctx.sync()

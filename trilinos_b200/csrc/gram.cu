@@ -203,6 +203,67 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1)
 }
 
 // ---------------------------------------------------------------------------------------------
+// Skinny variant: one vector against p <= 8 columns.  DGKS' findBasis orthogonalises column j of
+// the new block against columns 0..j-1 one column at a time (BelosDGKSOrthoManager.hpp:1345-1480):
+// 3 such calls per config-2 iteration, each over a few L2-resident columns.  The TMA ring moves
+// boxes one column wide for them (2 KB per copy, ~18 us per call); here every thread simply has
+// all its 256-bit loads in flight at once (~5 us).
+template <int PMAX>
+__global__ void __launch_bounds__(256)
+    gram_skinny_kernel(const double* __restrict__ A, int64_t lda, int p, const double* __restrict__ v,
+                       int64_t n, double alpha, double* __restrict__ ws, unsigned int* ticket,
+                       double* __restrict__ out, uint64_t* flag, uint64_t seq) {
+  constexpr int kW = 8;
+  const int64_t nvec = (n + 3) >> 2;
+  double acc[PMAX][2];
+#pragma unroll
+  for (int j = 0; j < PMAX; ++j) acc[j][0] = acc[j][1] = 0.0;
+  for (int64_t i = blockIdx.x * 256ll + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * 256) {
+    const int64_t r = 4 * i;
+    double4v vb = ld_keep4(v + r);
+    double4v va[PMAX];
+#pragma unroll
+    for (int j = 0; j < PMAX; ++j)
+      if (j < p) va[j] = ld_keep4(A + (size_t)j * lda + r);
+    const bool m1 = r + 1 < n, m2 = r + 2 < n, m3 = r + 3 < n;  // padding rows of the last vector
+    if (!m3) {
+      if (!m1) vb.y = 0.0;
+      if (!m2) vb.z = 0.0;
+      vb.w = 0.0;
+    }
+#pragma unroll
+    for (int j = 0; j < PMAX; ++j)
+      if (j < p) {
+        if (!m3) {
+          if (!m1) va[j].y = 0.0;
+          if (!m2) va[j].z = 0.0;
+          va[j].w = 0.0;
+        }
+        acc[j][0] = fma(va[j].x, vb.x, acc[j][0]);
+        acc[j][1] = fma(va[j].y, vb.y, acc[j][1]);
+        acc[j][0] = fma(va[j].z, vb.z, acc[j][0]);
+        acc[j][1] = fma(va[j].w, vb.w, acc[j][1]);
+      }
+  }
+  __shared__ double sm[kW][PMAX];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < PMAX; ++j) {
+    const double t = warp_sum(acc[j][0] + acc[j][1]);
+    if (lane == 0) sm[warp][j] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x < p) {
+    double t = sm[0][threadIdx.x];
+#pragma unroll
+    for (int w = 1; w < kW; ++w) t += sm[w][threadIdx.x];
+    ws[(size_t)threadIdx.x * gridDim.x + blockIdx.x] = alpha * t;
+  }
+  if (!fold_partials_wide<kW>(ws, ticket, p, gridDim.x, blockIdx.x, 1, out)) return;
+  publish_flag(flag, seq);
+}
+
+// ---------------------------------------------------------------------------------------------
 // FP64 tensor-core (DMMA) variant for q = 8 / 16 right-hand sides.
 //
 // At q = 16 the Gram needs 2 q / 8 = 4 flop per streamed byte, i.e. ~26 TFLOP/s to stay on the HBM
@@ -396,6 +457,25 @@ static EncodeTiledFn encode_tiled_fn() {
 // box = rows x cols; out-of-bounds elements read as zero
 int make_tmap(CUtensorMap* tm, const double* base, int64_t n, int ncols, int64_t ld, int box_rows,
               int box_cols) {
+  // The encode is a pure function of its arguments and costs a driver call on the critical path of
+  // every Gram / update (the host waits for the result right after): keep the last few descriptors.
+  struct Entry {
+    const double* base = nullptr;
+    int64_t n = 0, ld = 0;
+    int ncols = 0, box_rows = 0, box_cols = 0;
+    CUtensorMap tm;
+  };
+  constexpr int kSlots = 256;
+  static thread_local Entry cache[kSlots];
+  uint64_t h = reinterpret_cast<uint64_t>(base) >> 8;
+  h = (h ^ (uint64_t)ncols * 0x9E3779B97F4A7C15ull ^ (uint64_t)box_rows * 0xC2B2AE3D27D4EB4Full ^
+       (uint64_t)box_cols * 0x165667B19E3779F9ull);
+  Entry& e = cache[(h ^ (h >> 17) ^ (h >> 31)) % kSlots];
+  if (e.base == base && e.n == n && e.ld == ld && e.ncols == ncols && e.box_rows == box_rows &&
+      e.box_cols == box_cols) {
+    *tm = e.tm;
+    return 0;
+  }
   EncodeTiledFn enc = encode_tiled_fn();
   if (!enc) return fail(B200_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
   const cuuint64_t dims[2] = {(cuuint64_t)n, (cuuint64_t)ncols};
@@ -408,6 +488,8 @@ int make_tmap(CUtensorMap* tm, const double* base, int64_t n, int ncols, int64_t
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return failf(B200_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  e.base = base; e.n = n; e.ld = ld; e.ncols = ncols; e.box_rows = box_rows; e.box_cols = box_cols;
+  e.tm = *tm;
   return 0;
 }
 
@@ -496,6 +578,18 @@ int launch_gram_dmma(Ctx* ctx, const double* A, int64_t lda, int p, const double
   return 0;
 }
 
+template <int PMAX>
+int launch_gram_skinny(Ctx* ctx, const double* A, int64_t lda, int p, const double* v, int64_t n,
+                       double alpha, double* out, uint64_t* flag) {
+  const int64_t nvec = (n + 3) / 4;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nvec + 511) / 512, ctx->num_sms * 4));
+  gram_skinny_kernel<PMAX><<<grid, 256, 0, ctx->stream>>>(A, lda, p, v, n, alpha, ctx->ws, ctx->ticket,
+                                                          out, flag, ctx->seq);
+  ++ctx->launches;
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace
 
 int launch_gram(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, int64_t ldv, int q,
@@ -516,7 +610,15 @@ int launch_gram(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, 
       const char* e = getenv("B200_GRAM_DMMA");
       return !(e && e[0] == '0');
     }();
-    if (step == 16 && dmma_on)
+    static const bool skinny_on = [] {
+      const char* e = getenv("B200_SKINNY");
+      return !(e && e[0] == '0');
+    }();
+    if (q == 1 && p <= 8 && skinny_on) {
+      if (p <= 2) rc = launch_gram_skinny<2>(ctx, A, lda, p, Vk, n, alpha, outk, flag);
+      else if (p <= 4) rc = launch_gram_skinny<4>(ctx, A, lda, p, Vk, n, alpha, outk, flag);
+      else rc = launch_gram_skinny<8>(ctx, A, lda, p, Vk, n, alpha, outk, flag);
+    } else if (step == 16 && dmma_on)
       rc = launch_gram_dmma<2>(ctx, A, lda, p, Vk, ldv, n, alpha, outk, ldc, flag);
     else if (step == 8 && dmma_on)
       rc = launch_gram_dmma<1>(ctx, A, lda, p, Vk, ldv, n, alpha, outk, ldc, flag);
