@@ -15,7 +15,16 @@ Xe = tb.dist.local_multivec(ctx, n, lo, hi, b, zero=False); Xe.MvRandom()
 B = tb.dist.local_multivec(ctx, n, lo, hi, b); op.Apply(Xe, B)
 X = tb.dist.local_multivec(ctx, n, lo, hi, b)
 mgr = tb.BlockGmresSolMgr(op, block_size=b, num_blocks=m, max_iters=m * cycles, max_restarts=100000, tol=tol, ortho=ortho)
+import os
+timing = os.environ.get("B200_CYCLE_TIMING") == "1"   # per-kernel-class CUDA-event times (adds event overhead)
+if timing:
+    ctx.timing_read(reset=True); ctx.timing_enable(True)
 l0, s0 = ctx.counters()
 r = mgr.solve(X, B)
 l1, s1 = ctx.counters()
-print(json.dumps(dict(workload=wl, iters=r["num_iters"], seconds=r["solve_seconds"], launches=l1 - l0, syncs=s1 - s0)))
+out = dict(workload=wl, iters=r["num_iters"], seconds=r["solve_seconds"], launches=l1 - l0, syncs=s1 - s0)
+if timing:
+    ctx.timing_enable(False)
+    out["classes"] = {k: dict(calls=v["calls"], ms=round(v["ms"], 2), GBps=round(v["bytes"] / max(v["ms"], 1e-9) / 1e6, 1))
+                      for k, v in ctx.timing_read(reset=True).items() if v["calls"]}
+print(json.dumps(out))
