@@ -278,7 +278,8 @@ __global__ void __launch_bounds__(256)
 // doubles per 8 x 8 block, so a warp keeps the accumulators of all (up to 8) column blocks of a
 // pass in registers (12 consumer warps + the producer = 13 warps, at most 4 per SM sub-partition,
 // so each thread may use 128 registers).  Shared-memory fill traffic == algorithmic bytes, and the TMA rows stay long
-// (R * 8 >= 1 KB).  12 consumer warps = 4 column tiles (8 columns of A) x 3 row groups; fragment
+// (R * 8 >= 1 KB).  12 consumer warps = 4 column tiles (8 columns of A) x 3 row groups (a narrower
+// last block gets fewer column tiles and more row groups); fragment
 // lane l = (row 4 step + l%4, column 8 tile + l/4); R = 4 (mod 16) makes the column stride 8 banks
 // (mod 32): every fragment load is two conflict-free wavefronts.
 constexpr int kMaxCB = 8;   // 32-column blocks per pass (256 columns)
@@ -345,12 +346,11 @@ __global__ void __launch_bounds__(13 * 32, 1)
     }
     __syncwarp();
   } else {
-    // wfull / 8 column tiles x NW / (wfull / 8) row groups (4 x 3 for a full block)
-    const int nmt = wfull >> 3, nrg = NW / nmt;
-    const int mt = warp % nmt, rg = warp / nmt;
+    // per column block: ceil(width / 8) column tiles x NW / tiles row groups (4 x 3 for a full
+    // block, 1 x 12 for a last block of <= 8 columns: every warp has work in every stage)
     const uint32_t colstride = (uint32_t)R * 8u;
     const uint32_t frag = (uint32_t)(lane >> 2) * colstride + (uint32_t)(lane & 3) * 8u;
-    const uint32_t a_off = smem_u32(stage0) + (uint32_t)(8 * mt) * colstride + frag;
+    const uint32_t a_off = smem_u32(stage0) + frag;
     const uint32_t v_off = smem_u32(vbuf0) + frag;
     const int nsteps = R >> 2;
     int s = 0, vb = 0;
@@ -371,8 +371,10 @@ __global__ void __launch_bounds__(13 * 32, 1)
           if (i < ncbp) {
             mbar_wait(&full_bar[s], ph);
             // columns >= p of the last block are zero-filled by the TMA unit
-            if (rg < nrg && 8 * mt < min(kTC, g.p - (cb0 + i) * kTC)) {
-              const uint32_t ast = a_off + (uint32_t)s * a_bytes;
+            const int nmt = (min(kTC, g.p - (cb0 + i) * kTC) + 7) >> 3, nrg = NW / nmt;
+            const int mt = warp % nmt, rg = warp / nmt;
+            if (rg < nrg) {
+              const uint32_t ast = a_off + (uint32_t)(8 * mt) * colstride + (uint32_t)s * a_bytes;
               for (int step = rg; step < nsteps; step += nrg) {
                 const uint32_t row = (uint32_t)step * 32u;  // 4 rows x 8 bytes
                 const double a = lds_f64(ast + row);
@@ -402,8 +404,10 @@ __global__ void __launch_bounds__(13 * 32, 1)
         if (i < ncbp) {
           const int col0 = (cb0 + i) * kTC;
           const int wdt = min(kTC, g.p - col0);
+          const int nmt = (wdt + 7) >> 3, nrg = NW / nmt, wb = 8 * nmt;
+          const int mt = warp % nmt, rg = warp / nmt;
           if (rg < nrg) {
-            double* r = red + ((size_t)rg * wfull + 8 * mt + (lane >> 2)) * Q + 2 * (lane & 3);
+            double* r = red + ((size_t)rg * wb + 8 * mt + (lane >> 2)) * Q + 2 * (lane & 3);
 #pragma unroll
             for (int nt = 0; nt < NTQ; ++nt) {
               r[8 * nt] = c[i][nt][0];
@@ -414,7 +418,7 @@ __global__ void __launch_bounds__(13 * 32, 1)
           for (int e = threadIdx.x; e < wdt * Q; e += NW * 32) {
             const int cc = e / Q, k = e % Q;
             double sres = 0.0;
-            for (int r = 0; r < nrg; ++r) sres += red[((size_t)r * wfull + cc) * Q + k];
+            for (int r = 0; r < nrg; ++r) sres += red[((size_t)r * wb + cc) * Q + k];
             g.ws[(size_t)blockIdx.x * (size_t)(g.p * g.q) + (size_t)k * g.p + col0 + cc] = sres;
           }
           consumer_bar<NW * 32>();
