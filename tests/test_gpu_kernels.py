@@ -98,7 +98,7 @@ def test_scale_init_random(ctx, n):
 
 
 @pytest.mark.parametrize("n", [1, 5, 127, 1000, 4097, 100003])
-@pytest.mark.parametrize("p,q", [(1, 1), (3, 1), (4, 4), (5, 3), (7, 5), (33, 4), (40, 8), (100, 4), (9, 16), (64, 2), (300, 16), (70, 8), (20, 24), (2, 1), (4, 1), (7, 1), (8, 1), (9, 1)])
+@pytest.mark.parametrize("p,q", [(1, 1), (3, 1), (4, 4), (5, 3), (7, 5), (33, 4), (40, 8), (100, 4), (9, 16), (64, 2), (300, 16), (70, 8), (20, 24), (2, 1), (4, 1), (7, 1), (8, 1), (9, 1), (40, 12), (33, 13)])
 def test_trans_mv(ctx, n, p, q):
     a, v = rnd(n, p, 9), rnd(n, q, 10)
     A, V = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, v)

@@ -601,19 +601,22 @@ int launch_gram(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, 
   if (p <= 0 || q <= 0) return 0;
   double* out = ctx->result_ptr() + out_off;
   ctx->t_begin(K_GRAM, 8.0 * n * ((double)p + q));
-  // q is processed in one pass whenever q <= 16 (Q = next supported width; unused accumulator
-  // columns are masked), so A is streamed from HBM exactly once per call
+  // q <= 8 and q = 16 are one pass over A (Q = next supported width; unused accumulator columns
+  // are masked)
   int k0 = 0;
   int rc = 0;
   while (k0 < q && rc == 0) {
-    const int step = std::min(16, q - k0);
     const double* Vk = V + (size_t)k0 * ldv;
     double* outk = out + (size_t)k0 * ldc;
-    uint64_t* flag = (last && k0 + step >= q) ? ctx->result_flag() : nullptr;
     static const bool dmma_on = [] {
       const char* e = getenv("B200_GRAM_DMMA");
       return !(e && e[0] == '0');
     }();
+    // 16 and 8 columns go to the DMMA kernel; 9..15 are split 8 + rest (two passes over A beat the
+    // 16-wide SIMT kernel, which spills and reaches 37 % of the HBM peak)
+    const int rem = q - k0;
+    const int step = rem >= 16 ? 16 : (rem > 8 && dmma_on ? 8 : rem);
+    uint64_t* flag = (last && k0 + step >= q) ? ctx->result_flag() : nullptr;
     static const bool skinny_on = [] {
       const char* e = getenv("B200_SKINNY");
       return !(e && e[0] == '0');
