@@ -859,6 +859,7 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
         HaloWait hw;
         hp.npeers = hw.n = (int)op->peers.size();
         hw.seq = hs;
+        hw.err = ctx->flag_d + 1;
         for (int pi = 0; pi < hp.npeers; ++pi) {
           const HaloPeer& pr = op->peers[pi];
           const size_t rhalf = ((size_t)pr.remote_nghost * op->buf_k * sizeof(double) + 255) / 256 * 256;

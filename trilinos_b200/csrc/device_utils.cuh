@@ -284,5 +284,27 @@ __device__ __forceinline__ void consumer_bar() {
 }
 
 
+
+// Acquire-spin on a flag another GPU raises over NVLink.  A peer that never arrives (a rank that
+// died or left the collective call sequence) must not hang this GPU: after ~30 s the wait gives
+// up, records it in the host-visible error word and returns false.
+__device__ __forceinline__ bool spin_acquire_sys(const uint64_t* flag, uint64_t want, uint64_t* err) {
+  uint64_t v, t0 = 0;
+  uint32_t it = 0;
+  while (true) {
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flag) : "memory");
+    if (v >= want) return true;
+    if ((++it & 0xfffu) == 0) {
+      uint64_t now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 30000000000ull) {
+        if (err) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(err), "l"((uint64_t)1) : "memory");
+        return false;
+      }
+    }
+  }
+}
+
 }  // namespace b200
 #endif

@@ -152,7 +152,9 @@ namespace {
 template <bool IS_MAX>
 __global__ void __launch_bounds__(256)
     xchg_publish_kernel(XchgWindow w, const double* __restrict__ src, double* __restrict__ dst,
-                        int count, uint64_t xseq, uint64_t* flag, uint64_t seq) {
+                        int count, uint64_t xseq, uint64_t* flag, uint64_t seq, uint64_t* err) {
+  __shared__ int timed_out;
+  if (threadIdx.x == 0) timed_out = 0;
   const int par = (int)(xseq & 1u);
   const int P = w.nranks, me = w.rank;
   for (int r = 0; r < P; ++r) {
@@ -166,12 +168,10 @@ __global__ void __launch_bounds__(256)
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pf), "l"(xseq) : "memory");
     const uint64_t* mf = reinterpret_cast<const uint64_t*>(static_cast<char*>(w.win[me]) + par * 256) +
                          threadIdx.x;
-    uint64_t v;
-    do {
-      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mf) : "memory");
-    } while (v < xseq);
+    if (!spin_acquire_sys(mf, xseq, err)) timed_out = 1;
   }
   __syncthreads();
+  if (timed_out) return;  // nothing is published: the host sees the error word
   const double* mine = reinterpret_cast<const double*>(static_cast<char*>(w.win[me]) + kXchgFlagBytes) +
                        (size_t)par * kMaxPeers * kXchgMax;
   for (int i = threadIdx.x; i < count; i += blockDim.x) {
@@ -191,10 +191,10 @@ int launch_xchg_publish(Ctx* ctx, const double* src_d, double* dst, int count, b
   ++ctx->xseq;
   if (is_max)
     xchg_publish_kernel<true><<<1, 256, 0, ctx->stream>>>(ctx->xw, src_d, dst, count, ctx->xseq,
-                                                         ctx->flag_d, seq);
+                                                         ctx->flag_d, seq, ctx->flag_d + 1);
   else
     xchg_publish_kernel<false><<<1, 256, 0, ctx->stream>>>(ctx->xw, src_d, dst, count, ctx->xseq,
-                                                          ctx->flag_d, seq);
+                                                          ctx->flag_d, seq, ctx->flag_d + 1);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
   return 0;

@@ -199,6 +199,8 @@ int Ctx::wait_flag(uint64_t s) {
     if (*flag_h >= s) break;
     _mm_pause();
     if ((++spins & 0xfffff) == 0) {
+      if (flag_h[1] != 0)  // a peer-memory wait on the device gave up (spin_acquire_sys)
+        return fail(B200_ERR_TIMEOUT, "a peer GPU did not arrive at an exchange within 30 s");
       cudaError_t e = cudaStreamQuery(stream);
       if (e != cudaSuccess && e != cudaErrorNotReady)
         return failf(B200_ERR_CUDA, "device error while waiting for a reduction: %s",

@@ -228,6 +228,7 @@ struct HaloWait {
   int n = 0;
   const uint64_t* flag[kMaxPeers];
   uint64_t seq = 0;
+  uint64_t* err = nullptr;   // host-visible error word (set when a neighbour never arrives)
 };
 
 struct Op {

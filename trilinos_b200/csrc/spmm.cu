@@ -277,10 +277,7 @@ __global__ void __launch_bounds__(256)
                      double* __restrict__ y, int64_t ldy, HaloWait w) {
   if (w.n > 0) {  // peer-memory halo: wait until every neighbour's put of this apply has landed
     if ((int)threadIdx.x < w.n) {
-      uint64_t v;
-      do {
-        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(w.flag[threadIdx.x]) : "memory");
-      } while (v < w.seq);
+      spin_acquire_sys(w.flag[threadIdx.x], w.seq, w.err);  // on timeout: host sees the error word
     }
     __syncthreads();
   }
