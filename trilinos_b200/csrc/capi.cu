@@ -331,6 +331,7 @@ extern "C" int b200_mv_dot(const b200_mv* mv, const b200_mv* A, double* b, int n
     return 0;
   }
   ++ctx->seq;
+  ctx->plan_reduction(k, false);
   for (int j = 0; j < k;) {
     const int len = run_length(j, k, mv, j, A, j);
     B200_TRY(launch_dot(ctx, mv->col(j), mv->ld, A->col(j), A->ld, mv->n_local, len, j,
@@ -370,6 +371,7 @@ extern "C" int b200_mv_norm(const b200_mv* mv, int type, double* normvec, int nn
     }
   }
   ++ctx->seq;
+  ctx->plan_reduction(k, type == B200_NORM_INF);
   for (int j = 0; j < k;) {
     const int len = run_length(j, k, mv, j);
     B200_TRY(launch_norm(ctx, mv->col(j), mv->ld, mv->n_local, len, type, j, j + len >= k));
@@ -401,6 +403,7 @@ extern "C" int b200_mv_trans_mv(const b200_mv* mv, double alpha, const b200_mv* 
     return fail(B200_ERR_ARG, "MvTransMv: result block larger than the host mailbox");
   Ctx* ctx = mv->ctx;
   ++ctx->seq;
+  ctx->plan_reduction(p * q, false);
   for (int jv = 0; jv < q;) {
     const int lv = run_length(jv, q, mv, jv);
     for (int ja = 0; ja < p;) {

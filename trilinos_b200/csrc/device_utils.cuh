@@ -306,5 +306,48 @@ __device__ __forceinline__ bool spin_acquire_sys(const uint64_t* flag, uint64_t 
   }
 }
 
+
+// Hand a finished reduction to the host (see XchgPub in runtime.cuh).  Called by every thread of
+// the finishing CTA; results of this launch were stored by this CTA, those of earlier launches of
+// the same reduction by earlier kernels on the stream.
+template <class Pub>
+__device__ __forceinline__ void publish_result(const Pub& pb) {
+  if (pb.nranks <= 1) {
+    publish_flag(pb.flag, pb.seq);
+    return;
+  }
+  constexpr int kFlagBytes = 512, kMaxR = 8, kSlot = 4096;  // kXchgFlagBytes, kMaxPeers, kXchgMax
+  __shared__ int timed_out;
+  if (threadIdx.x == 0) timed_out = 0;
+  __syncthreads();
+  const int par = (int)(pb.xseq & 1u), P = pb.nranks, me = pb.rank;
+  for (int r = 0; r < P; ++r) {
+    double* slot = reinterpret_cast<double*>(static_cast<char*>(pb.win[r]) + kFlagBytes) +
+                   ((size_t)par * kMaxR + me) * kSlot;
+    for (int i = threadIdx.x; i < pb.count; i += blockDim.x) slot[i] = pb.src[i];
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < P) {
+    uint64_t* pf = reinterpret_cast<uint64_t*>(static_cast<char*>(pb.win[threadIdx.x]) + par * 256) + me;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pf), "l"(pb.xseq) : "memory");
+    const uint64_t* mf =
+        reinterpret_cast<const uint64_t*>(static_cast<char*>(pb.win[me]) + par * 256) + threadIdx.x;
+    if (!spin_acquire_sys(mf, pb.xseq, pb.err)) timed_out = 1;
+  }
+  __syncthreads();
+  if (timed_out) return;
+  const double* mine = reinterpret_cast<const double*>(static_cast<char*>(pb.win[me]) + kFlagBytes) +
+                       (size_t)par * kMaxR * kSlot;
+  for (int i = threadIdx.x; i < pb.count; i += blockDim.x) {
+    double t = __ldcg(mine + i);
+    for (int r = 1; r < P; ++r) {
+      const double v = __ldcg(mine + (size_t)r * kSlot + i);
+      t = pb.is_max ? fmax(t, v) : t + v;
+    }
+    pb.dst[i] = t;
+  }
+  publish_flag(pb.flag, pb.seq);
+}
+
 }  // namespace b200
 #endif

@@ -61,8 +61,7 @@ struct GramArgs {
   unsigned int* ticket;
   double* out;       // C(:, 0..q) with leading dimension ldc
   int ldc;
-  uint64_t* flag;
-  uint64_t seq;
+  XchgPub pub;       // how the finishing CTA hands the result to the host
 };
 
 // Q: accumulator columns (>= q), CPW: columns of A per warp, NW: consumer warps.
@@ -199,7 +198,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1)
                                             g.out[(size_t)k * g.ldc + col] = g.alpha * sres;
                                           });
   if (!fin) return;
-  publish_flag(g.flag, g.seq);
+  publish_result(g.pub);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -212,7 +211,7 @@ template <int PMAX>
 __global__ void __launch_bounds__(256)
     gram_skinny_kernel(const double* __restrict__ A, int64_t lda, int p, const double* __restrict__ v,
                        int64_t n, double alpha, double* __restrict__ ws, unsigned int* ticket,
-                       double* __restrict__ out, uint64_t* flag, uint64_t seq) {
+                       double* __restrict__ out, const XchgPub pub) {
   constexpr int kW = 8;
   const int64_t nvec = (n + 3) >> 2;
   double acc[PMAX][2];
@@ -260,7 +259,7 @@ __global__ void __launch_bounds__(256)
     ws[(size_t)threadIdx.x * gridDim.x + blockIdx.x] = alpha * t;
   }
   if (!fold_partials_wide<kW>(ws, ticket, p, gridDim.x, blockIdx.x, 1, out)) return;
-  publish_flag(flag, seq);
+  publish_result(pub);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -434,7 +433,7 @@ __global__ void __launch_bounds__(13 * 32, 1)
                                             g.out[(size_t)k * g.ldc + col] = g.alpha * sres;
                                           });
   if (!fin) return;
-  publish_flag(g.flag, g.seq);
+  publish_result(g.pub);
 }
 
 }  // namespace
@@ -501,7 +500,7 @@ namespace {
 
 template <int Q, int CPW, int NW>
 int launch_gram_t(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, int64_t ldv, int q,
-                  int64_t n, double alpha, double* out, int ldc, uint64_t* flag) {
+                  int64_t n, double alpha, double* out, int ldc, const XchgPub& pub) {
   static_assert(kTC % CPW == 0 && NW >= kTC / CPW, "one column block must fit the consumer warps");
   GramArgs g;
   g.A = A; g.V = V; g.lda = lda; g.ldv = ldv; g.n = n; g.p = p; g.q = q;
@@ -517,7 +516,7 @@ int launch_gram_t(Ctx* ctx, const double* A, int64_t lda, int p, const double* V
   g.nstage = (int)std::max<size_t>(2, std::min<size_t>(kMaxStages, kSmemBudget / stage_bytes));
   g.ntiles = (n + R - 1) / R;
   g.alpha = alpha;
-  g.ws = ctx->ws; g.ticket = ctx->ticket; g.out = out; g.ldc = ldc; g.flag = flag; g.seq = ctx->seq;
+  g.ws = ctx->ws; g.ticket = ctx->ticket; g.out = out; g.ldc = ldc; g.pub = pub;
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->num_sms, g.ntiles));
   if ((size_t)p * q * (grid + grid / 16 + 1) * sizeof(double) > kWorkspaceBytes)
     return fail(B200_ERR_ARG, "MvTransMv: partial-sum workspace too small");
@@ -539,7 +538,7 @@ int launch_gram_t(Ctx* ctx, const double* A, int64_t lda, int p, const double* V
 
 template <int NTQ>
 int launch_gram_dmma(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, int64_t ldv,
-                     int64_t n, double alpha, double* out, int ldc, uint64_t* flag) {
+                     int64_t n, double alpha, double* out, int ldc, const XchgPub& pub) {
   constexpr int Q = 8 * NTQ;
   GramArgs g;
   g.A = A; g.V = V; g.lda = lda; g.ldv = ldv; g.n = n; g.p = p; g.q = Q;
@@ -562,7 +561,7 @@ int launch_gram_dmma(Ctx* ctx, const double* A, int64_t lda, int p, const double
   }
   g.ntiles = (n + R - 1) / R;
   g.alpha = alpha;
-  g.ws = ctx->ws; g.ticket = ctx->ticket; g.out = out; g.ldc = ldc; g.flag = flag; g.seq = ctx->seq;
+  g.ws = ctx->ws; g.ticket = ctx->ticket; g.out = out; g.ldc = ldc; g.pub = pub;
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->num_sms, g.ntiles));
   if ((size_t)p * Q * (grid + grid / 16 + 1) * sizeof(double) > kWorkspaceBytes)
     return fail(B200_ERR_ARG, "MvTransMv: partial-sum workspace too small");
@@ -584,11 +583,11 @@ int launch_gram_dmma(Ctx* ctx, const double* A, int64_t lda, int p, const double
 
 template <int PMAX>
 int launch_gram_skinny(Ctx* ctx, const double* A, int64_t lda, int p, const double* v, int64_t n,
-                       double alpha, double* out, uint64_t* flag) {
+                       double alpha, double* out, const XchgPub& pub) {
   const int64_t nvec = (n + 3) / 4;
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nvec + 511) / 512, ctx->num_sms * 4));
   gram_skinny_kernel<PMAX><<<grid, 256, 0, ctx->stream>>>(A, lda, p, v, n, alpha, ctx->ws, ctx->ticket,
-                                                          out, flag, ctx->seq);
+                                                          out, pub);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
   return 0;
@@ -616,7 +615,7 @@ int launch_gram(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, 
     // 16-wide SIMT kernel, which spills and reaches 37 % of the HBM peak)
     const int rem = q - k0;
     const int step = rem >= 16 ? 16 : (rem > 8 && dmma_on ? 8 : rem);
-    uint64_t* flag = (last && k0 + step >= q) ? ctx->result_flag() : nullptr;
+    const XchgPub flag = ctx->make_pub(last && k0 + step >= q);
     static const bool skinny_on = [] {
       const char* e = getenv("B200_SKINNY");
       return !(e && e[0] == '0');

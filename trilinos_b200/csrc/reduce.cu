@@ -15,6 +15,9 @@ namespace b200 {
 
 namespace {
 
+// publish_result() (device_utils.cuh) restates the window layout
+static_assert(kXchgFlagBytes == 512 && kMaxPeers == 8 && kXchgMax == 4096, "window layout");
+
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 
@@ -24,7 +27,7 @@ template <int OP>
 __global__ void __launch_bounds__(kThreads)
     colreduce_kernel(const double* __restrict__ a, int64_t lda, const double* __restrict__ b,
                      int64_t ldb, int64_t n, double* __restrict__ ws, unsigned int* ticket,
-                     double* __restrict__ out, uint64_t* flag, uint64_t seq) {
+                     double* __restrict__ out, const XchgPub pub) {
   const int col = blockIdx.y;
   const double* ac = a + (size_t)col * lda;
   const double* bc = (OP == RED_DOT) ? b + (size_t)col * ldb : nullptr;
@@ -72,7 +75,7 @@ __global__ void __launch_bounds__(kThreads)
   if (!fold_partials_wide<kWarps, OP == RED_MAXABS>(ws, ticket, gridDim.y, gridDim.x, blockIdx.x,
                                                      gridDim.y, out))
     return;
-  publish_flag(flag, seq);
+  publish_result(pub);
 }
 
 inline dim3 red_grid(int64_t n, int k) {
@@ -91,15 +94,15 @@ int launch_dot(Ctx* ctx, const double* a, int64_t lda, const double* b, int64_t 
   if (k <= 0) return 0;
   const dim3 g = red_grid(n, k);
   double* out = ctx->result_ptr() + out_off;
-  uint64_t* flag = last ? ctx->result_flag() : nullptr;
+  const XchgPub pub = ctx->make_pub(last);
   const bool self = (a == b && lda == ldb);
   ctx->t_begin(K_REDUCE, (self ? 8.0 : 16.0) * n * k);
   if (self)
     colreduce_kernel<RED_DOT_SELF><<<g, kThreads, 0, ctx->stream>>>(
-        a, lda, nullptr, 0, n, ctx->ws, ctx->ticket, out, flag, ctx->seq);
+        a, lda, nullptr, 0, n, ctx->ws, ctx->ticket, out, pub);
   else
     colreduce_kernel<RED_DOT><<<g, kThreads, 0, ctx->stream>>>(a, lda, b, ldb, n, ctx->ws,
-                                                                ctx->ticket, out, flag, ctx->seq);
+                                                                ctx->ticket, out, pub);
   ctx->t_end();
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
@@ -111,20 +114,20 @@ int launch_norm(Ctx* ctx, const double* a, int64_t lda, int64_t n, int k, int ty
   if (k <= 0) return 0;
   const dim3 g = red_grid(n, k);
   double* out = ctx->result_ptr() + out_off;
-  uint64_t* flag = last ? ctx->result_flag() : nullptr;
+  const XchgPub pub = ctx->make_pub(last);
   ctx->t_begin(K_REDUCE, 8.0 * n * k);
   switch (type) {
     case B200_NORM_ONE:
       colreduce_kernel<RED_ABS><<<g, kThreads, 0, ctx->stream>>>(a, lda, nullptr, 0, n, ctx->ws,
-                                                                  ctx->ticket, out, flag, ctx->seq);
+                                                                  ctx->ticket, out, pub);
       break;
     case B200_NORM_TWO:
       colreduce_kernel<RED_DOT_SELF><<<g, kThreads, 0, ctx->stream>>>(
-          a, lda, nullptr, 0, n, ctx->ws, ctx->ticket, out, flag, ctx->seq);
+          a, lda, nullptr, 0, n, ctx->ws, ctx->ticket, out, pub);
       break;
     default:
       colreduce_kernel<RED_MAXABS><<<g, kThreads, 0, ctx->stream>>>(
-          a, lda, nullptr, 0, n, ctx->ws, ctx->ticket, out, flag, ctx->seq);
+          a, lda, nullptr, 0, n, ctx->ws, ctx->ticket, out, pub);
       break;
   }
   ctx->t_end();

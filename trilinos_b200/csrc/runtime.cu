@@ -250,8 +250,44 @@ bool Ctx::recall_dot(uint64_t a, uint64_t b, double* val, int* rc) {
   return false;
 }
 
+void Ctx::plan_reduction(int count, bool is_max) {
+  static const bool on = [] {
+    const char* e = std::getenv("B200_FUSE_XCHG");
+    return !(e && e[0] == '0');
+  }();
+  xplan_count = count;
+  xplan_max = is_max;
+  xplan_ok = on && nranks > 1 && p2p && count <= kXchgMax;
+  xplan_done = false;
+}
+
+XchgPub Ctx::make_pub(bool last) {
+  XchgPub pb;
+  pb.seq = seq;
+  if (!last) return pb;
+  if (nranks <= 1) {
+    pb.flag = flag_d;
+    return pb;
+  }
+  if (!xplan_ok) return pb;  // finish_reduction() launches the exchange (or the NCCL allreduce)
+  pb.flag = flag_d;
+  pb.nranks = nranks;
+  pb.rank = rank;
+  pb.count = xplan_count;
+  pb.is_max = xplan_max ? 1 : 0;
+  pb.xseq = ++xseq;
+  pb.src = red_d;
+  pb.dst = mbox_d;
+  pb.err = flag_d + 1;
+  for (int i = 0; i < nranks; ++i) pb.win[i] = xw.win[i];
+  xplan_done = true;
+  return pb;
+}
+
 int Ctx::finish_reduction(int count, bool is_max) {
-  if (nranks > 1) {
+  const bool done = xplan_done;
+  xplan_ok = xplan_done = false;
+  if (nranks > 1 && !done) {
     if (p2p && count <= kXchgMax) {
       B200_TRY(launch_xchg_publish(this, red_d, mbox_d, count, is_max, seq));
     } else {

@@ -59,6 +59,22 @@ struct XchgWindow {
   int nranks = 1, rank = 0;
 };
 
+// How the finishing CTA of a reduction kernel hands its result to the host.  nranks <= 1: release
+// `flag` with `seq` (results were written straight into the mailbox).  nranks > 1: run the
+// peer-memory exchange of reduce.cu in this CTA (put src[0..count) into every rank's window, wait
+// for the peers, fold in rank order into dst = mailbox) and then release the flag -- the separate
+// exchange kernel and its launch gap disappear from the critical path of every reduction.
+struct XchgPub {
+  uint64_t* flag = nullptr;
+  uint64_t seq = 0;
+  int nranks = 1, rank = 0, count = 0, is_max = 0;
+  uint64_t xseq = 0;
+  const double* src = nullptr;
+  double* dst = nullptr;
+  uint64_t* err = nullptr;
+  void* win[kMaxPeers] = {};
+};
+
 // where a kernel with a fused reduction epilogue puts its column dot products
 struct FusedDots {
   double* out = nullptr;        // device-visible mailbox slot (nullptr: no epilogue)
@@ -149,6 +165,12 @@ struct Ctx {
   // multi-rank: allreduce red_d[0..count) (sum or max) then publish to mailbox; single-rank:
   // the kernel already wrote the mailbox.  Returns after the host can read mbox_h.
   int finish_reduction(int count, bool is_max);
+  // announce the size of the reduction whose kernels are launched next (after ++seq), so that the
+  // last of them can run the peer exchange itself (make_pub(true))
+  void plan_reduction(int count, bool is_max);
+  XchgPub make_pub(bool last);
+  int xplan_count = 0;
+  bool xplan_max = false, xplan_ok = false, xplan_done = false;
   double* result_ptr() { return nranks > 1 ? red_d : mbox_d; }
   uint64_t* result_flag() { return nranks > 1 ? nullptr : flag_d; }
 };
