@@ -6,6 +6,10 @@
 //   -> Epetra_MultiVector::Multiply('T','N',alpha,A,V,0)   epetra/src/Epetra_MultiVector.cpp:1936-2083
 //   -> local DGEMM + Reduce() (SumAll)                     :2400-2433
 //
+// Three kernels share the launch interface (launch_gram): gram_tma_kernel (q <= 4 right-hand sides,
+// SIMT FP64, described next), gram_dmma_kernel (q = 8 / 16, FP64 tensor cores, further down) and
+// gram_skinny_kernel (one vector against <= 8 columns).
+//
 // Design (HBM-bound, algorithmic bytes 8 n (p + q)).  The first version of this kernel kept the
 // streamed operand in registers (8 x 32-byte loads per thread per step) and reached only ~40 % of
 // the HBM roofline: with ~64 KB in flight per SM the kernel is latency-, not bandwidth-bound.
