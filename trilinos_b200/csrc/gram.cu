@@ -73,7 +73,7 @@ struct GramArgs {
 // (2 per lane, one conflict-free LDS.128 per column) per substep.
 template <int Q, int CPW, int NW>
 __global__ void __launch_bounds__((NW + 1) * 32, 1)
-    gram_tma_kernel(const GramArgs g, const __grid_constant__ CUtensorMap tmA,
+    gram_tma_kernel(const __grid_constant__ GramArgs g, const __grid_constant__ CUtensorMap tmA,
                     const __grid_constant__ CUtensorMap tmV) {
   constexpr int NT = (NW + 1) * 32;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -215,7 +215,7 @@ template <int PMAX>
 __global__ void __launch_bounds__(256)
     gram_skinny_kernel(const double* __restrict__ A, int64_t lda, int p, const double* __restrict__ v,
                        int64_t n, double alpha, double* __restrict__ ws, unsigned int* ticket,
-                       double* __restrict__ out, const XchgPub pub) {
+                       double* __restrict__ out, const __grid_constant__ XchgPub pub) {
   constexpr int kW = 8;
   const int64_t nvec = (n + 3) >> 2;
   double acc[PMAX][2];
@@ -289,7 +289,7 @@ constexpr int kMaxCB = 8;   // 32-column blocks per pass (256 columns)
 
 template <int NTQ>  // q == 8 * NTQ
 __global__ void __launch_bounds__(13 * 32, 1)
-    gram_dmma_kernel(const GramArgs g, const __grid_constant__ CUtensorMap tmA,
+    gram_dmma_kernel(const __grid_constant__ GramArgs g, const __grid_constant__ CUtensorMap tmA,
                      const __grid_constant__ CUtensorMap tmV) {
   constexpr int NW = 12, NT = (NW + 1) * 32, Q = 8 * NTQ;
   extern __shared__ __align__(128) unsigned char smem_raw[];

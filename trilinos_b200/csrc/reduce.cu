@@ -27,7 +27,7 @@ template <int OP>
 __global__ void __launch_bounds__(kThreads)
     colreduce_kernel(const double* __restrict__ a, int64_t lda, const double* __restrict__ b,
                      int64_t ldb, int64_t n, double* __restrict__ ws, unsigned int* ticket,
-                     double* __restrict__ out, const XchgPub pub) {
+                     double* __restrict__ out, const __grid_constant__ XchgPub pub) {
   const int col = blockIdx.y;
   const double* ac = a + (size_t)col * lda;
   const double* bc = (OP == RED_DOT) ? b + (size_t)col * ldb : nullptr;
