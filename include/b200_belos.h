@@ -37,7 +37,7 @@ extern "C" {
 #define B200_ERR_NCCL (-5)
 #define B200_ERR_ALIAS (-6)
 #define B200_ERR_UNSUPPORTED (-7)
-#define B200_ERR_TIMEOUT (-8)
+#define B200_ERR_TIMEOUT (-8)    /* a reduction result or a peer GPU's exchange flag did not arrive (120 s / 30 s) */
 
 /* Belos::NormType (belos/src/BelosTypes.hpp) */
 #define B200_NORM_ONE 0
