@@ -9,6 +9,12 @@ one batch of right-hand sides.  N=1 workload = BASELINE configs[1] (Galeri Lapla
 4, 50 blocks, DGKS).  N>1 (launched by torchrun, one rank per GPU): the SAME problem, rows block-
 partitioned over the ranks (strong scaling), halo exchange + small allreduces over NCCL.
 
+Before anything is timed, every run checks the path it is about to measure against the serial CPU oracle at two
+small sizes (`parity_check`; the run exits non-zero if it fails).  After the config-2 measurement the default run
+also measures BASELINE configs[2] (Laplace3D 200^3, the 8M-row strong-scaling problem; `north_star_8m`) and the first
+restart cycle of configs[4] (Recirc2D 2000^2, b=16, restart 100; `c5_cycle`) at the same N; `value` / `config` stay on
+config 2.
+
 JSON line (rank 0): value = block iterations / s with inputs resident in HBM (CUDA events on the
 compute stream, max over ranks); e2e = the same through the C-ABI with HOST buffers (pinned host ->
 device copy of B and X0, solve, device -> host copy of X inside the timed region); roofline = the
@@ -17,7 +23,7 @@ instrumented step after the timed ones (so the event records do not perturb `val
 cpu_baseline = the reference's own Epetra/Belos code (oracle/_ref) on the host cores, bounded sample.
 
 `--impl reference`: the reference's own CPU implementation (oracle/_ref: Epetra + Belos compiled
-from the reference sources; Epetra OpenMP loops + threaded BLAS on all host cores), each step =
+from the reference sources; Epetra OpenMP loops + threaded BLAS on all physical host cores), each step =
 the first restart cycle (Num Blocks block iterations) of the same solve.
 """
 import argparse
@@ -101,25 +107,29 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def best_threads(solve_probe):
-    """The reference gets the thread count that serves it best on this host (probe: a few block
-    iterations per candidate); small problems run fastest on one thread, config-2-sized ones on all."""
+def ref_threads():
+    """Thread count of the reference arm: ALL PHYSICAL CORES of the host (one documented choice, the same in the
+    reference arm and in cpu_baseline; a per-run timing probe moved the headline ratio by 25 % in round 1)."""
     from oracle import ref
-    cores = ref.max_threads()
-    best, best_t = 1, None
-    for th in sorted({1, max(1, cores // 2), cores}):
-        ref.set_threads(th)
-        t0 = time.perf_counter()
-        solve_probe()
-        dt = time.perf_counter() - t0
-        if best_t is None or dt < best_t:
-            best, best_t = th, dt
-    ref.set_threads(best)
-    return best
+    try:
+        import psutil
+        cores = psutil.cpu_count(logical=False) or ref.max_threads()
+    except ImportError:
+        cores = ref.max_threads()
+    cores = max(1, min(int(cores), ref.max_threads()))
+    ref.set_threads(cores)
+    return cores
+
+
+def config_of(wl, n):
+    """The workload description -- byte-identical in the B200 arm and the reference arm."""
+    name, dims, b, m, ortho, tol, cfg = WORKLOADS[wl]
+    return {"workload": wl, "baseline_config": cfg, "matrix": name, "dims": list(dims), "n": n, "block_size": b,
+            "num_blocks": m, "ortho": ortho, "tol": tol}
 
 
 def reference_arm(args, wl):
-    """The reference's own CPU implementation of the path (oracle/_ref), all host threads."""
+    """The reference's own CPU implementation of the path (oracle/_ref), all physical host cores."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
@@ -133,8 +143,7 @@ def reference_arm(args, wl):
     xe, _ = ref.random(1, n, b)
     B = ref.apply(rp, ci, va, xe)
     sample_iters = m  # one restart cycle: the basis grows 0 -> b*m, i.e. every kernel shape of the solve
-    cores = best_threads(lambda: ref.block_gmres(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=min(m, 8),
-                                                 max_restarts=1000, tol=tol, ortho=ortho))
+    cores = ref_threads()
 
     def step():
         _, r = ref.block_gmres(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=sample_iters, max_restarts=1000,
@@ -152,13 +161,12 @@ def reference_arm(args, wl):
     wall = time.perf_counter() - t0
     val = iters / secs
     sample = (f"first restart cycle ({sample_iters} block iterations, basis width 0->{b * m}) of the {wl} solve, "
-              f"Epetra OpenMP loops + OpenBLAS 0.3.15 on {cores} of {ref.max_threads()} host threads (best of 1/half/all)")
+              f"Epetra OpenMP loops + OpenBLAS 0.3.15 on {cores} threads (all physical cores; {ref.max_threads()} logical)")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * wall / max(args.steps, 1), "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": wl, "baseline_config": cfg, "matrix": name, "dims": list(dims), "n": n, "block_size": b,
-                   "num_blocks": m, "ortho": ortho, "tol": tol},
+        "config": config_of(wl, n),
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -181,14 +189,154 @@ def cpu_baseline(wl):
     n, rp, ci, va = _ref_matrix(name, dims)
     xe, _ = ref.random(1, n, b)
     B = ref.apply(rp, ci, va, xe)
-    cores = best_threads(lambda: ref.block_gmres(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=min(m, 8),
-                                                 max_restarts=1000, tol=tol, ortho=ortho))
+    cores = ref_threads()
     _, r = ref.block_gmres(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=m, max_restarts=1000, tol=tol, ortho=ortho)
     ref.set_threads(1)
     return {"value": r["num_iters"] / r["solve_seconds"], "unit": UNIT, "cores": cores, "kind": "reference",
             "sample": f"first restart cycle ({r['num_iters']} block iterations, basis width 0->{b * m}) of the same solve; "
-                      f"reference Epetra/Belos (oracle/_ref), Epetra OpenMP + OpenBLAS on {cores} of {ref.max_threads()} host threads (best of 1/half/all), "
+                      f"reference Epetra/Belos (oracle/_ref), Epetra OpenMP + OpenBLAS on {cores} threads (all physical cores), "
                       f"{r['solve_seconds']:.1f} s"}
+
+
+def parity_block(tb, ctx, rank, world):
+    """Untimed multi-GPU parity check (the body of tests/_nccl_worker.py at two small sizes): MvRandom partition
+    independence, Apply / MvTransMv / MvDot / MvNorm of the distributed path against the serial CPU oracle on the same
+    global inputs.  The oracle is the CHECKER here, outside every timed region.  Returns (max_rel_err, ok)."""
+    import numpy as np
+    import torch
+    import oracle
+    worst, ok = 0.0, True
+
+    def rel(a, r):
+        return float(np.linalg.norm(np.ravel(a - r)) / max(np.linalg.norm(np.ravel(r)), 1e-300))
+
+    for name, dims, k in (("Laplace3D", (24, 24, 8 * max(world, 3)), 4), ("Recirc2D", (41, 16 * max(world, 3), 1), 16)):
+        op, n, lo, hi = tb.dist.local_operator(ctx, name, dims)
+        ng, rp, ci, va = oracle.galeri_csr(name, *dims)
+        xg, _ = oracle.random(1, n, k)
+        ctx.set_seed(1)
+        X = tb.dist.local_multivec(ctx, n, lo, hi, k, zero=False)
+        X.MvRandom()
+        if not np.array_equal(X.to_numpy(), xg[lo:hi]):
+            ok = False
+        Y = tb.dist.local_multivec(ctx, n, lo, hi, k)
+        yg = oracle.spmm(rp, ci.astype(np.int32), va, xg)
+        op.Apply(X, Y)
+        op.Apply(X, Y)
+        errs = [rel(Y.to_numpy(), yg[lo:hi]), rel(Y.MvTransMv(1.0, X), oracle.trans_mv(1.0, xg, yg)),
+                rel(Y.MvDot(X), oracle.dot(yg, xg)), rel(Y.MvNorm(tb.NORM_TWO), oracle.norm(yg, 1)),
+                rel(Y.MvNorm(tb.NORM_INF), oracle.norm(yg, 2))]
+        worst = max(worst, max(errs))
+        del op, X, Y
+    t = torch.tensor([worst, 0.0 if ok else 1.0], dtype=torch.float64, device=f"cuda:{ctx.device}")
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    worst, bad = float(t[0].item()), float(t[1].item())
+    return worst, (bad == 0.0 and worst <= 1e-13)
+
+
+class Workload:
+    """One workload set up on this rank: operator, X_exact (Epetra LCG, seed 1), B = A X_exact, X, solver manager."""
+
+    def __init__(self, tb, ctx, wl, max_iters=-1, max_restarts=100000):
+        name, dims, b, m, ortho, tol, cfg = WORKLOADS[wl]
+        self.tb, self.ctx, self.wl, self.b, self.m, self.tol = tb, ctx, wl, b, m, tol
+        self.op, self.n, self.lo, self.hi = tb.dist.local_operator(ctx, name, dims)
+        self.nloc = self.hi - self.lo
+        ctx.set_seed(1)
+        self.Xe = tb.dist.local_multivec(ctx, self.n, self.lo, self.hi, b, zero=False)
+        self.Xe.MvRandom()                       # Epetra LCG, seed 1, partition-independent stream
+        self.B = tb.dist.local_multivec(ctx, self.n, self.lo, self.hi, b)
+        self.op.Apply(self.Xe, self.B)
+        self.X = tb.dist.local_multivec(ctx, self.n, self.lo, self.hi, b)
+        self.mgr = tb.BlockGmresSolMgr(self.op, block_size=b, num_blocks=m, max_iters=max_iters, max_restarts=max_restarts,
+                                       tol=tol, ortho=ortho)
+
+    def solve_resident(self):
+        self.X.MvInit(0.0)
+        return self.mgr.solve(self.X, self.B)
+
+
+def measure(torch, w, rank, world, steps, warmup, barrier, stream, must_converge=True, sample_clocks=False):
+    """value (device-timed, inputs resident), e2e (host buffers through the C-ABI), per-class roofline."""
+    import ctypes as C
+    import numpy as np
+    from trilinos_b200._lib import check, lib, c_dbl
+    tb, ctx, b, nloc = w.tb, w.ctx, w.b, w.nloc
+    dev = f"cuda:{ctx.device}"
+
+    def maxr(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- value: inputs resident in HBM --------------------------------------------------------
+    for _ in range(warmup):
+        r = w.solve_resident()
+    if must_converge and (not r["converged"] or max(r["true_rel_resid"]) > w.tol * 1.001):
+        raise SystemExit(f"{w.wl}: solve did not converge: {r}")
+    barrier()
+    sampler = ClockSampler(ctx.device) if (rank == 0 and sample_clocks) else None
+    l0, s0 = ctx.counters()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    iters = 0
+    e0.record(stream)
+    for _ in range(steps):
+        r = w.solve_resident()
+        iters += r["num_iters"]
+    e1.record(stream)
+    barrier()
+    l1, s1 = ctx.counters()
+    clocks = sampler.stop() if sampler else None
+    ms = maxr(e0.elapsed_time(e1))
+    value = iters / (ms * 1e-3)
+
+    # ---- e2e: host buffers through the C-ABI ---------------------------------------------------
+    Bh = torch.empty((b, nloc), dtype=torch.float64).pin_memory()      # column-major n x b
+    X0h = torch.zeros((b, nloc), dtype=torch.float64).pin_memory()
+    Xh = torch.empty((b, nloc), dtype=torch.float64).pin_memory()
+    Bh.numpy()[:] = w.B.to_numpy().T
+    P = C.POINTER(c_dbl)
+    Bd = tb.dist.local_multivec(ctx, w.n, w.lo, w.hi, b, zero=False)
+    Xd = tb.dist.local_multivec(ctx, w.n, w.lo, w.hi, b, zero=False)
+    ldh = max(nloc, 1)
+
+    def solve_e2e():
+        check(lib.b200_mv_copy_from_host(Bd._h, C.cast(Bh.data_ptr(), P), ldh))
+        check(lib.b200_mv_copy_from_host(Xd._h, C.cast(X0h.data_ptr(), P), ldh))
+        rr = w.mgr.solve(Xd, Bd)
+        check(lib.b200_mv_copy_to_host(Xd._h, C.cast(Xh.data_ptr(), P), ldh))
+        return rr
+
+    solve_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_iters = 0
+    for _ in range(steps):
+        e2e_iters += solve_e2e()["num_iters"]
+    barrier()
+    e2e_val = e2e_iters / maxr(time.perf_counter() - t0)
+    err = float(np.abs(Xh.numpy().T - w.Xe.to_numpy()).max())
+
+    # ---- roofline: one extra instrumented step (CUDA events around every launch) ---------------
+    ctx.timing_read(reset=True)
+    ctx.timing_enable(True)
+    w.solve_resident()
+    ctx.timing_enable(False)
+    tm = ctx.timing_read(reset=True)
+    peak, peak_src = peaks()
+    kern = {}
+    for k, v in tm.items():
+        if v["calls"]:
+            gbs = v["bytes"] / (v["ms"] * 1e-3) / 1e9 if v["ms"] > 0 else 0.0
+            kern[k] = {"calls": v["calls"], "ms": round(v["ms"], 3), "algorithmic_GB": round(v["bytes"] / 1e9, 3),
+                       "GBps": round(gbs, 1), "frac": round(gbs / peak, 3)}
+    return {"value": value, "ms": ms, "iters_per_solve": r["num_iters"], "converged": bool(r["converged"]),
+            "clocks": clocks, "gpu_launches": int(l1 - l0), "host_syncs": int(s1 - s0), "max_abs_err_vs_x_exact": err,
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(2 * nloc * b * 8 * world),
+                    "d2h_bytes_per_step": int(nloc * b * 8 * world)},
+            "kernels": kern, "peak": peak, "peak_src": peak_src}
 
 
 def main():
@@ -199,12 +347,12 @@ def main():
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the north_star_8m / c5_cycle secondary measurements")
     args = ap.parse_args()
     wl = args.workload or "laplace3d_100_b4"
     if args.impl == "reference":
         return reference_arm(args, wl)
 
-    import numpy as np
     import torch
     import trilinos_b200 as tb
     name, dims, b, m, ortho, tol, cfg = WORKLOADS[wl]
@@ -222,90 +370,16 @@ def main():
             torch.distributed.barrier()
         torch.cuda.synchronize()
 
-    op, n, lo, hi = tb.dist.local_operator(ctx, name, dims)
-    nloc = hi - lo
-    ctx.set_seed(1)
-    Xe = tb.dist.local_multivec(ctx, n, lo, hi, b, zero=False)
-    Xe.MvRandom()                       # Epetra LCG, seed 1, partition-independent stream
-    B = tb.dist.local_multivec(ctx, n, lo, hi, b)
-    op.Apply(Xe, B)
-    X = tb.dist.local_multivec(ctx, n, lo, hi, b)
-    mgr = tb.BlockGmresSolMgr(op, block_size=b, num_blocks=m, max_iters=-1, max_restarts=100000, tol=tol, ortho=ortho)
+    # ---- untimed parity block of the distributed path (every N; at N = 1 it checks the single-GPU path) ----------
+    perr, pok = parity_block(tb, ctx, rank, world)
+    if not pok:
+        if rank == 0:
+            print(json.dumps({"metric": METRIC, "parity_check": {"max_rel_err": perr, "ok": False}}))
+        raise SystemExit(f"parity block failed: max relative error {perr:.3e} (tolerance 1e-13)")
 
-    def solve_resident():
-        X.MvInit(0.0)
-        return mgr.solve(X, B)
-
-    # ---- value: inputs resident in HBM --------------------------------------------------------
-    for _ in range(warmup):
-        r = solve_resident()
-    if not r["converged"] or max(r["true_rel_resid"]) > tol * 1.001:
-        raise SystemExit(f"solve did not converge: {r}")
-    barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    l0, s0 = ctx.counters()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    iters = 0
-    e0.record(stream)
-    for _ in range(args.steps):
-        r = solve_resident()
-        iters += r["num_iters"]
-    e1.record(stream)
-    barrier()
-    l1, s1 = ctx.counters()
-    clocks = sampler.stop() if sampler else None
-    ms = e0.elapsed_time(e1)
-    t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local_rank}")
-    if world > 1:
-        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-    ms = float(t.item())
-    value = iters / (ms * 1e-3)
-
-    # ---- e2e: host buffers through the C-ABI ---------------------------------------------------
-    Bh = torch.empty((b, nloc), dtype=torch.float64).pin_memory()      # column-major n x b
-    X0h = torch.zeros((b, nloc), dtype=torch.float64).pin_memory()
-    Xh = torch.empty((b, nloc), dtype=torch.float64).pin_memory()
-    Bh.numpy()[:] = B.to_numpy().T
-    import ctypes as C
-    from trilinos_b200._lib import check, lib, c_dbl
-    P = C.POINTER(c_dbl)
-    Bd = tb.dist.local_multivec(ctx, n, lo, hi, b, zero=False)
-    Xd = tb.dist.local_multivec(ctx, n, lo, hi, b, zero=False)
-    ldh = max(nloc, 1)
-
-    def solve_e2e():
-        check(lib.b200_mv_copy_from_host(Bd._h, C.cast(Bh.data_ptr(), P), ldh))
-        check(lib.b200_mv_copy_from_host(Xd._h, C.cast(X0h.data_ptr(), P), ldh))
-        rr = mgr.solve(Xd, Bd)
-        check(lib.b200_mv_copy_to_host(Xd._h, C.cast(Xh.data_ptr(), P), ldh))
-        return rr
-
-    solve_e2e()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_iters = 0
-    for _ in range(args.steps):
-        e2e_iters += solve_e2e()["num_iters"]
-    barrier()
-    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local_rank}")
-    if world > 1:
-        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-    e2e_val = e2e_iters / float(t.item())
-    err = float(np.abs(Xh.numpy().T - Xe.to_numpy()).max())
-
-    # ---- roofline: one extra instrumented step (CUDA events around every launch) ---------------
-    ctx.timing_read(reset=True)
-    ctx.timing_enable(True)
-    solve_resident()
-    ctx.timing_enable(False)
-    tm = ctx.timing_read(reset=True)
-    peak, peak_src = peaks()
-    kern = {}
-    for k, v in tm.items():
-        if v["calls"]:
-            gbs = v["bytes"] / (v["ms"] * 1e-3) / 1e9 if v["ms"] > 0 else 0.0
-            kern[k] = {"calls": v["calls"], "ms": round(v["ms"], 3), "algorithmic_GB": round(v["bytes"] / 1e9, 3),
-                       "GBps": round(gbs, 1), "frac": round(gbs / peak, 3)}
+    w = Workload(tb, ctx, wl)
+    res = measure(torch, w, rank, world, args.steps, warmup, barrier, stream, sample_clocks=True)
+    kern, peak = res["kernels"], res["peak"]
     dom = max(kern, key=lambda k: kern[k]["ms"]) if kern else None
     roofline = None
     if dom:
@@ -320,22 +394,44 @@ def main():
                 traffic = traffic_detail["dram_bytes"]
         roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
                     "frac": kern[dom]["frac"], "traffic": traffic, "traffic_detail": traffic_detail,
-                    "peak_source": peak_src, "launches": kern[dom]["calls"], "kernels": kern}
+                    "peak_source": res["peak_src"], "launches": kern[dom]["calls"], "kernels": kern}
+    nloc = w.nloc
+    out = {
+        "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
+        "ms_per_step": res["ms"] / max(args.steps, 1), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": config_of(wl, w.n),
+        "run_info": {"iters_per_solve": res["iters_per_solve"],
+                     "l2": "inputs larger than L2 (Krylov basis %.2f GB per GPU)" % (nloc * 8.0 * b * (m + 1) / 1e9),
+                     "partition": f"1-D row blocks over {world} rank(s)", "max_abs_err_vs_x_exact": res["max_abs_err_vs_x_exact"]},
+        "parity_check": {"max_rel_err": perr, "ok": True, "tolerance": 1e-13,
+                         "what": "untimed: MvRandom partition independence, Apply / MvTransMv / MvDot / MvNorm of the "
+                                 f"{world}-rank path vs the serial CPU oracle (Laplace3D k=4, Recirc2D k=16)"},
+        "clocks": res["clocks"], "gpu_launches": res["gpu_launches"], "host_syncs": res["host_syncs"],
+        "e2e": res["e2e"], "roofline": roofline,
+    }
+    del w
+
+    # ---- secondary measurements: the workloads north_star names beyond config 2 -------------------------------------
+    if not args.no_extras and args.workload is None:
+        # (a) the 8M-row strong-scaling problem (BASELINE configs[2]) at this N
+        w8 = Workload(tb, ctx, "laplace3d_200_b4")
+        r8 = measure(torch, w8, rank, world, 2, 2, barrier, stream)
+        out["north_star_8m"] = {"config": config_of("laplace3d_200_b4", w8.n), "value": r8["value"], "unit": UNIT,
+                                "steps": 2, "warmup": 2, "iters_per_solve": r8["iters_per_solve"], "e2e": r8["e2e"],
+                                "gpu_launches": r8["gpu_launches"], "host_syncs": r8["host_syncs"],
+                                "max_abs_err_vs_x_exact": r8["max_abs_err_vs_x_exact"], "roofline": {"kernels": r8["kernels"]}}
+        del w8
+        # (b) BASELINE configs[4] (Recirc2D 2000^2, b=16, restart 100): its first restart cycle (100 block iterations)
+        w5 = Workload(tb, ctx, "recirc2d_2000_b16", max_iters=100, max_restarts=0)
+        r5 = measure(torch, w5, rank, world, 1, 1, barrier, stream, must_converge=False)
+        out["c5_cycle"] = {"config": config_of("recirc2d_2000_b16", w5.n), "value": r5["value"], "unit": UNIT,
+                           "sample": "first restart cycle: 100 block iterations, basis width 0->1600", "steps": 1, "warmup": 1,
+                           "e2e": r5["e2e"], "gpu_launches": r5["gpu_launches"], "host_syncs": r5["host_syncs"],
+                           "roofline": {"kernels": r5["kernels"]}}
+        del w5
 
     if rank == 0:
-        out = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
-            "ms_per_step": ms / max(args.steps, 1), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic",
-            "config": {"workload": wl, "baseline_config": cfg, "matrix": name, "dims": list(dims), "n": n, "block_size": b,
-                       "num_blocks": m, "ortho": ortho, "tol": tol, "iters_per_solve": r["num_iters"],
-                       "l2": "inputs larger than L2 (Krylov basis %.2f GB per GPU)" % (nloc * 8.0 * b * (m + 1) / 1e9),
-                       "partition": f"1-D row blocks over {world} rank(s)", "max_abs_err_vs_x_exact": err},
-            "clocks": clocks, "gpu_launches": int(l1 - l0), "host_syncs": int(s1 - s0),
-            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(2 * nloc * b * 8 * world),
-                    "d2h_bytes_per_step": int(nloc * b * 8 * world)},
-            "roofline": roofline,
-        }
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(wl)
         print(json.dumps(out))

@@ -38,6 +38,8 @@ extern "C" {
 #define B200_ERR_ALIAS (-6)
 #define B200_ERR_UNSUPPORTED (-7)
 #define B200_ERR_TIMEOUT (-8)    /* a reduction result or a peer GPU's exchange flag did not arrive (120 s / 30 s) */
+#define B200_ERR_BELOS (-9)      /* a Belos exception that did not come from a C-ABI status (orthogonalisation
+                                    failure, LinearProblem / status-test errors); solver library only */
 
 /* Belos::NormType (belos/src/BelosTypes.hpp) */
 #define B200_NORM_ONE 0
@@ -49,6 +51,8 @@ typedef struct b200_mv b200_mv;   /* multivector (owning, or view sharing storag
 typedef struct b200_op b200_op;   /* row-block distributed CSR operator */
 
 const char* b200_last_error(void);
+/* status code that came with b200_last_error() (thread-local; 0 if no call has failed yet) */
+int b200_last_status(void);
 const char* b200_version(void);
 
 /* ------------------------------------------------------------------ context
@@ -182,6 +186,16 @@ int b200_halo_recv_plan(int nranks, int64_t n_ghost, const int32_t* ghost_owner,
                         int64_t* recv_off);
 int b200_halo_send_index(int64_t n_global, int nranks, int rank, int64_t n_asked,
                          const int64_t* asked_gids, int32_t* send_idx);
+
+/* Host-only: the tile plan the window-staged SpMM kernel (trilinos_b200/csrc/spmm_win.cu) streams, for a local
+ * CSR block with local column ids (>= n_local: ghost columns) -- exported so that the CPU tests can replay
+ * the kernel's arithmetic from the plan and compare it with Epetra_CrsMatrix::GeneralMM's row sums
+ * (epetra/src/Epetra_CrsMatrix.cpp:3516-3534) bit for bit.  rows_per_tile: 128 | 256.  Two-call protocol:
+ * tiles_out / blob_out NULL -> sizes only (ntiles x 128-byte descriptors, blob_bytes).  Returns 0, or 1 if the
+ * format does not apply to this matrix (more than 8 x-runs per tile, rows longer than 255, > 25 % padding). */
+int b200_spmm_window_plan(int64_t n_local, int64_t n_ghost, const int32_t* rowptr, const int32_t* colind_local,
+                          const double* values, int rows_per_tile, int64_t* ntiles, int64_t* blob_bytes,
+                          int32_t* blob_cap, int32_t* wcap, void* tiles_out, void* blob_out);
 
 /* Galeri-style generators (galeri/src-epetra/Galeri_CrsMatrices.cpp:273-416,
  * CrsMatrices/Galeri_Cross2D.h, Galeri_Cross3D.h, Galeri_Recirc2D.h;

@@ -69,6 +69,19 @@ int b200_belos_solve(const char* solver, b200_op* A, b200_mv* X, b200_mv* B,
 int b200_belos_solve_prec(const char* solver, b200_op* A, b200_cheby* prec, int left, b200_mv* X,
                           b200_mv* B, const b200_gmres_params* p, b200_gmres_result* r);
 
+/* b200_belos_solve_prec that also records, for solver "BlockGmres", the native residual norms Belos
+ * holds before every block iteration (Iteration::getNativeResiduals, belos/src/BelosBlockGmresIter.hpp:542-557)
+ * through a status test attached with BlockGmresSolMgr::setDebugStatusTest (BelosBlockGmresSolMgr.hpp:240):
+ * hist[row * numrhs + j], row = block iteration; *hist_rows = rows recorded (may exceed hist_cap_rows,
+ * only the first hist_cap_rows are stored).  Host data only: no extra kernel, same iteration.
+ *
+ * Status of the three solve entry points: 0, or the status of the C-ABI call that failed underneath
+ * (B200_ERR_CUDA / _NCCL / _TIMEOUT / _SHAPE ...), B200_ERR_BELOS for exceptions raised by Belos itself,
+ * B200_ERR_ARG for bad arguments / parameters. */
+int b200_belos_solve_hist(const char* solver, b200_op* A, b200_cheby* prec, int left, b200_mv* X,
+                          b200_mv* B, const b200_gmres_params* p, b200_gmres_result* r,
+                          double* hist, int hist_cap_rows, int* hist_rows);
+
 /* Runs Belos::TestMultiVecTraits and Belos::TestOperatorTraits (the reference's contract test)
  * on a B200MultiVec of n rows x ncols columns and a tridiagonal B200CrsOp. 0 = passed. */
 int b200_belos_mvop_test(b200_ctx* ctx, int n, int ncols, int verbose);

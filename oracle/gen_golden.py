@@ -4,6 +4,7 @@ oracle/_ref); the fixtures are committed and travel to the GPU box.
 
     python oracle/gen_golden.py            # kernel + small-solve fixtures (seconds)
     python oracle/gen_golden.py --full     # additionally BASELINE config 1/2-sized solves (minutes)
+    python oracle/gen_golden.py --configs345   # BASELINE configs 3, 4 (full solves) and 5 (first restart cycle)
 
 Every array below is an output of reference code on explicit, seeded inputs:
   ref_galeri_*.npz   Galeri::CreateCrsMatrix on the "Linear" map                 (CSR, global ids)
@@ -219,6 +220,44 @@ def gen_solves(cases, fn, threads=1):
     ref.set_threads(1)
 
 
+# BASELINE configs 3-5 at full size, all host threads (Epetra OpenMP loops + threaded OpenBLAS), with the native
+# residual norms of every block iteration (ref.block_gmres_history).  Config 5 (Recirc2D 2000^2, b=16, m=100) is a
+# BOUNDED run -- its first restart cycle: a converged CPU solve is out of reach (1616 x 4M basis = 52 GB).
+# (label, matrix, dims, block size, num blocks, ortho, tol, max restarts, max iters)
+SOLVES_345 = [
+    ("config3_laplace3d_200_b4_dgks", "Laplace3D", (200, 200, 200), 4, 50, "DGKS", 1e-8, 1000, -1),
+    ("config4_brick3d_150_b8_icgs", "Brick3D", (150, 150, 150), 8, 50, "ICGS", 1e-8, 1000, -1),
+    ("config5_recirc2d_2000_b16_dgks_cycle1", "Recirc2D", (2000, 2000, 1), 16, 100, "DGKS", 1e-8, 1000, 100),
+]
+
+
+def gen_345(only=None):
+    path = os.path.join(OUT, "ref_solves_full.json")
+    res = json.load(open(path)) if os.path.exists(path) else {}
+    threads = ref.max_threads()
+    ref.set_threads(threads)
+    for label, name, dims, b, m, ortho, tol, maxr, max_iters in SOLVES_345:
+        if only and only not in label:
+            continue
+        kw = dict(conv=1.0, diff=1e-5) if name == "Recirc2D" else {}
+        n, rp, ci, va = matrix(name, dims, **kw)
+        xe, _ = ref.random(1, n, b)
+        B = ref.apply(rp, ci, va, xe)
+        X, r, hist = ref.block_gmres_history(rp, ci, va, B, block_size=b, num_blocks=m, max_iters=max_iters, max_restarts=maxr,
+                                             tol=tol, ortho=ortho)
+        r.update(matrix=name, dims=list(dims), block_size=b, num_blocks=m, ortho=ortho, tol=tol, max_restarts=maxr,
+                 max_iters=max_iters, solver="BlockGmres",
+                 rhs="X_exact = Epetra LCG seed 1 (column-major sweep), B = A X_exact, X0 = 0",
+                 max_abs_err=float(np.abs(X - xe).max()), threads=threads,
+                 native_resid_history=[[float(v) for v in row] for row in hist],
+                 history="row i = Iteration::getNativeResiduals before block iteration i (unscaled 2-norms per right-hand side)")
+        res[label] = r
+        print(label, r["num_iters"], r["converged"], f"{r['solve_seconds']:.2f}s", max(r["true_rel_resid"]), hist.shape, flush=True)
+        json.dump(res, open(path, "w"), indent=1, sort_keys=True)
+        del X, B, xe, rp, ci, va
+    ref.set_threads(1)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     if "--ingest" in sys.argv:
@@ -229,6 +268,9 @@ if __name__ == "__main__":
         gen_solves(SOLVES_MANAGERS, "ref_solves_managers.json")
     elif "--full" in sys.argv:
         gen_solves(SOLVES_FULL, "ref_solves_full.json", threads=1)
+    elif "--configs345" in sys.argv:  # optional: a substring selecting one case
+        i = sys.argv.index("--configs345")
+        gen_345(sys.argv[i + 1] if len(sys.argv) > i + 1 else None)
     else:
         gen_galeri()
         gen_kernels()

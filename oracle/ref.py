@@ -176,6 +176,26 @@ def block_gmres(rowptr, colind, values, B, X0=None, block_size=1, num_blocks=300
                    true_rel_resid=[r.true_rel_resid[i] for i in range(min(k, 64))])
 
 
+def block_gmres_history(rowptr, colind, values, B, X0=None, block_size=1, num_blocks=300, max_iters=-1, max_restarts=20,
+                        tol=1e-8, ortho="DGKS", max_rows=100000):
+    """block_gmres() with the native residual norms of every block iteration recorded (Belos::B200ResidualHistory
+    attached through BlockGmresSolMgr::setDebugStatusTest): returns (X, result dict, hist[rows, k])."""
+    rp, ci, va = _csr(rowptr, colind, values)
+    B = _F(B)
+    n, k = B.shape
+    X = np.zeros((n, k), order="F") if X0 is None else _F(X0).copy(order="F")
+    o = ortho.encode()
+    p = GmresParams(block_size, num_blocks, max_iters, max_restarts, tol, o, 0, -1, 1, 0, 0)
+    r = GmresResult()
+    hist = np.zeros((max_rows, k))
+    rows = C.c_int(0)
+    _ck(lib().ref_belos_solve_hist_csr(C.c_int64(n), _i32(rp), _i32(ci), _d(va), k, _d(B), C.c_int64(n), _d(X), C.c_int64(n),
+                                       C.byref(p), C.byref(r), _d(hist), max_rows, C.byref(rows)))
+    return X, dict(converged=bool(r.converged), num_iters=r.num_iters, achieved_tol=r.achieved_tol,
+                   loss_of_accuracy=bool(r.loss_of_accuracy), solve_seconds=r.solve_seconds,
+                   true_rel_resid=[r.true_rel_resid[i] for i in range(min(k, 64))]), hist[:min(rows.value, max_rows)].copy()
+
+
 def cheby_apply(rowptr, colind, values, X, degree=3, lambda_max=-1.0, eig_ratio=30.0, min_diag=0.0, eig_iters=10, seed=1):
     """Y = Ifpack_Chebyshev(A).ApplyInverse(X) (point mode, zero starting solution); returns (Y, lambda_max used)."""
     rp, ci, va = _csr(rowptr, colind, values)

@@ -26,6 +26,7 @@
 #include "BelosConfigDefs.hpp"
 #include "BelosEpetraAdapter.hpp"
 #include "BelosLinearProblem.hpp"
+#include "B200ResidualHistory.hpp"
 #include "Epetra_CrsMatrix.h"
 #include "Epetra_Map.h"
 #include "Epetra_MultiVector.h"
@@ -257,6 +258,9 @@ extern "C" int ref_belos_solve_csr(const char* solver_name, int64_t n, const int
                                    const ref_gmres_params* p, ref_gmres_result* r);
 struct ref_cheby_params;
 static const ref_cheby_params* g_cheby = nullptr;  // set by ref_belos_solve_cheby_csr
+// set by ref_belos_solve_hist_csr: native residual norms per block iteration ([row][rhs])
+static double* g_hist = nullptr;
+static int g_hist_cap = 0, g_hist_rows = 0;
 namespace {
 RCP<class Ifpack_Chebyshev> make_cheby(const RCP<Epetra_CrsMatrix>& A, const ref_cheby_params* c,
                                        double* lambda_used);
@@ -311,8 +315,16 @@ extern "C" int ref_belos_solve_csr(const char* solver_name, int64_t n, const int
     }
     Teuchos::TimeMonitor::zeroOutTimers();
     RCP<Belos::SolverManager<ST, MV, OP> > solver;
+    RCP<Belos::B200ResidualHistory<ST, MV, OP> > rec;
     if (which == "BlockGmres") {
-      solver = rcp(new Belos::BlockGmresSolMgr<ST, MV, OP>(rcp(&problem, false), rcp(&belosList, false)));
+      RCP<Belos::BlockGmresSolMgr<ST, MV, OP> > bg =
+          rcp(new Belos::BlockGmresSolMgr<ST, MV, OP>(rcp(&problem, false), rcp(&belosList, false)));
+      if (g_hist_cap > 0) {  // setProblem() makes solve() rebuild the status-test combo with the recorder in it
+        rec = rcp(new Belos::B200ResidualHistory<ST, MV, OP>());
+        bg->setDebugStatusTest(rec);
+        bg->setProblem(rcp(&problem, false));
+      }
+      solver = bg;
     } else if (which == "PseudoBlockGmres") {
       belosList.remove("Adaptive Block Size");
       belosList.remove("Flexible Gmres", false);
@@ -343,6 +355,7 @@ extern "C" int ref_belos_solve_csr(const char* solver_name, int64_t n, const int
     r->loss_of_accuracy = solver->isLOADetected() ? 1 : 0;
     r->solve_seconds = std::chrono::duration<double>(t1 - t0).count();
     r->num_rhs = numrhs;
+    if (nonnull(rec)) g_hist_rows = rec->copy_out(g_hist, g_hist_cap, numrhs);
     std::vector<double> actual(numrhs), rhs(numrhs);
     MV resid(map, numrhs);
     OPT::Apply(*A, *X, resid);
@@ -355,6 +368,22 @@ extern "C" int ref_belos_solve_csr(const char* solver_name, int64_t n, const int
   } catch (const std::exception& e) {
     return fail(e);
   }
+}
+
+// BlockGmres with the native residual norms of every block iteration recorded (B200ResidualHistory
+// attached through BlockGmresSolMgr::setDebugStatusTest): hist[row * numrhs + j], *rows = rows recorded
+extern "C" int ref_belos_solve_hist_csr(int64_t n, const int32_t* rowptr, const int32_t* colind,
+                                        const double* values, int numrhs, const double* Bh, int64_t ldb,
+                                        double* Xh, int64_t ldx, const ref_gmres_params* p,
+                                        ref_gmres_result* r, double* hist, int cap_rows, int* rows) {
+  g_hist = hist;
+  g_hist_cap = cap_rows;
+  g_hist_rows = 0;
+  const int rc = ref_belos_solve_csr("BlockGmres", n, rowptr, colind, values, numrhs, Bh, ldb, Xh, ldx, p, r);
+  if (rows) *rows = g_hist_rows;
+  g_hist = nullptr;
+  g_hist_cap = 0;
+  return rc;
 }
 
 // ---- Chebyshev right preconditioner: the reference's Ifpack_Chebyshev (ifpack/src/Ifpack_Chebyshev.cpp)

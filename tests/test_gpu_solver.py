@@ -25,7 +25,7 @@ def test_belos_mvop_tester(ctx, n, k):
     assert tb.mvop_test(ctx, n, k)
 
 
-def run_case(ctx, g):
+def run_case(ctx, g, history=0):
     name, dims, b = g["matrix"], g["dims"], g["block_size"]
     n, rp, ci, va = tb.galeri(name, *dims)
     op = tb.CrsOperator(ctx, n, 0, n, rp, ci, va)
@@ -36,8 +36,25 @@ def run_case(ctx, g):
     X = tb.MultiVec(ctx, n, b)
     mgr = tb.SOLVER_MANAGERS[g.get("solver", "BlockGmres")](op, block_size=b, num_blocks=g["num_blocks"], max_iters=g.get("max_iters", -1),
                               max_restarts=g["max_restarts"], tol=g["tol"], ortho=g["ortho"])
-    r = mgr.solve(X, B)
+    r = mgr.solve(X, B, history=history) if history else mgr.solve(X, B)
     return r, X.to_numpy(), xe
+
+
+# Relative tolerance on the native residual norms of a block iteration, GPU run vs reference run of the same solve.
+# The two runs differ only in summation order (1e-16-level perturbations of every inner product); over a restart
+# cycle GMRES amplifies those by at most the conditioning of the least-squares problem, far below this bound while
+# the residual has not stagnated.  Measured: see profiles/r2_fullsize_parity.txt.
+HIST_RTOL = 1e-8
+
+
+def check_history(r, g, rows=None):
+    ref = np.array(g["native_resid_history"])
+    got = np.array(r["native_resid_history"])
+    m = min(len(ref), len(got)) if rows is None else rows
+    assert m >= min(len(ref), 50), (len(ref), len(got))
+    rel = np.abs(got[:m] - ref[:m]) / np.maximum(np.abs(ref[:m]), 1e-300)
+    assert rel.max() <= HIST_RTOL, (float(rel.max()), np.unravel_index(rel.argmax(), rel.shape))
+    return float(rel.max())
 
 
 @pytest.mark.parametrize("label", sorted(SOLVES))
@@ -52,13 +69,26 @@ def test_iteration_count_parity_small(ctx, label):
 
 @pytest.mark.parametrize("label", sorted(FULL))
 def test_iteration_count_parity_baseline_configs(ctx, label):
-    """BASELINE configs[0] (Laplace2D 100^2, b=1) and configs[1] (Laplace3D 100^3, b=4, 50 blocks, DGKS) at full size."""
+    """All five BASELINE configs at FULL size on one GPU against runs of the reference's own Epetra/Belos code
+    (oracle/gen_golden.py --full / --configs345): configs[0] Laplace2D 100^2 b=1, configs[1] Laplace3D 100^3 b=4,
+    configs[2] Laplace3D 200^3 b=4 (8M rows), configs[3] Brick3D 150^3 b=8 ICGS -- iteration count within +-2 %,
+    same achieved tolerance, and (where the golden run recorded it) the native residual norms of the first restart
+    cycle within HIST_RTOL; configs[4] Recirc2D 2000^2 b=16 m=100 -- a bounded run on both sides: the first restart
+    cycle (100 block iterations), residual history within HIST_RTOL for every iteration."""
     g = FULL[label]
-    r, x, xe = run_case(ctx, g)
+    bounded = not g["converged"]                 # config 5: the reference run is its first restart cycle only
+    hist = g.get("native_resid_history")
+    r, x, xe = run_case(ctx, g, history=(len(hist) + 8) if hist else 0)
+    if bounded:
+        assert not r["converged"] and r["num_iters"] == g["num_iters"], (r["num_iters"], g["num_iters"])
+        check_history(r, g)
+        return
     assert r["converged"]
     assert max(r["true_rel_resid"]) <= g["tol"] * 1.001
     assert abs(r["num_iters"] - g["num_iters"]) <= max(1, round(0.02 * g["num_iters"])), (r["num_iters"], g["num_iters"])
     assert abs(r["achieved_tol"] - g["achieved_tol"]) <= 1e-3 * g["achieved_tol"] + 1e-12
+    if hist:
+        check_history(r, g, rows=min(len(hist), g["num_blocks"] + 1))
 
 
 @pytest.mark.parametrize("label", sorted(MANAGERS))

@@ -1,6 +1,6 @@
 """Kernel micro-benchmark at BASELINE config sizes (CUDA events on the compute stream).
 usage: python tools/kbench.py [n] [b]"""
-import sys, json
+import sys, json, os
 import numpy as np
 sys.path.insert(0, ".")
 import trilinos_b200 as tb
@@ -8,6 +8,7 @@ import oracle
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 b = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+PEAK = float(json.load(open("MEASURED_PEAKS.json"))["hbm_gbs"]) if os.path.exists("MEASURED_PEAKS.json") else 6650.0
 ctx = tb.Context(0)
 ctx.set_seed(1)
 PMAX = 200
@@ -31,7 +32,7 @@ def timed(name, fn, reps=20, flush=True):
         if v["calls"]:
             gbs = v["bytes"] / (v["ms"] * 1e-3) / 1e9
             res[name] = dict(cls=k, ms=v["ms"] / v["calls"], GBs=gbs)
-            print(f"{name:34s} {k:18s} {v['ms']/v['calls']*1e3:9.1f} us  {gbs:8.1f} GB/s  frac_of_6455={gbs/6454.9:.3f}", flush=True)
+            print(f"{name:34s} {k:18s} {v['ms']/v['calls']*1e3:9.1f} us  {gbs:8.1f} GB/s  frac_of_peak={gbs/PEAK:.3f}", flush=True)
 for p in (4, 16, 32, 64, 100, 200):
     Qp = Q.CloneView(list(range(p)))
     timed(f"trans_mv p={p} q={b}", lambda: X.MvTransMv(1.0, Qp))

@@ -38,6 +38,7 @@ P = C.POINTER
 
 _SIGS = {
     "b200_last_error": (C.c_char_p, []),
+    "b200_last_status": (C.c_int, []),
     "b200_version": (C.c_char_p, []),
     "b200_ctx_create": (C.c_int, [C.c_int, P(vp)]),
     "b200_ctx_destroy": (C.c_int, [vp]),
@@ -93,6 +94,8 @@ _SIGS = {
     "b200_build_colmap": (c_i64, [c_i64, C.c_int, C.c_int, c_i64, P(c_i64), P(c_i32), P(c_i64), P(c_i32)]),
     "b200_halo_recv_plan": (C.c_int, [C.c_int, c_i64, P(c_i32), P(c_i64), P(c_i64)]),
     "b200_halo_send_index": (C.c_int, [c_i64, C.c_int, C.c_int, c_i64, P(c_i64), P(c_i32)]),
+    "b200_spmm_window_plan": (C.c_int, [c_i64, c_i64, P(c_i32), P(c_i32), P(c_dbl), C.c_int, P(c_i64), P(c_i64),
+                                        P(c_i32), P(c_i32), vp, vp]),
     "b200_galeri_generate": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_int, c_dbl, c_dbl, c_i64, c_i64,
                                        P(c_i64), P(c_i32), P(c_i64), P(c_dbl)]),
 }

@@ -8,6 +8,7 @@
 #include <sstream>
 
 #include "B200BelosAdapter.hpp"
+#include "B200ResidualHistory.hpp"
 #include "BelosBlockCGSolMgr.hpp"
 #include "BelosBlockGmresSolMgr.hpp"
 #include "BelosPseudoBlockCGSolMgr.hpp"
@@ -57,6 +58,13 @@ extern "C" int b200_belos_solve(const char* solver_name, b200_op* A_h, b200_mv* 
 extern "C" int b200_belos_solve_prec(const char* solver_name, b200_op* A_h, b200_cheby* prec,
                                      int left, b200_mv* X_h, b200_mv* B_h,
                                      const b200_gmres_params* p, b200_gmres_result* r) {
+  return b200_belos_solve_hist(solver_name, A_h, prec, left, X_h, B_h, p, r, nullptr, 0, nullptr);
+}
+
+extern "C" int b200_belos_solve_hist(const char* solver_name, b200_op* A_h, b200_cheby* prec,
+                                     int left, b200_mv* X_h, b200_mv* B_h,
+                                     const b200_gmres_params* p, b200_gmres_result* r,
+                                     double* hist, int hist_cap_rows, int* hist_rows) {
   using Teuchos::RCP;
   using Teuchos::rcp;
   if (!solver_name || !A_h || !X_h || !B_h || !p || !r)
@@ -98,6 +106,8 @@ extern "C" int b200_belos_solve_prec(const char* solver_name, b200_op* A_h, b200
     int verbosity = Belos::Errors + Belos::Warnings + p->verbosity;
     if (p->show_timers) verbosity |= Belos::TimingDetails;
     belosList.set("Verbosity", verbosity);
+    // Belos' own messages (warnings, status-test output, timers) go to stderr: stdout stays the caller's
+    belosList.set("Output Stream", Teuchos::rcp(&std::cerr, false));
     if (p->output_frequency > 0) belosList.set("Output Frequency", p->output_frequency);
 
     Belos::LinearProblem<ST, MV, OP> problem(A, X, B);
@@ -113,8 +123,17 @@ extern "C" int b200_belos_solve_prec(const char* solver_name, b200_op* A_h, b200
     RCP<Belos::SolverManager<ST, MV, OP> > solver;
     RCP<Belos::LinearProblem<ST, MV, OP> > prob = rcp(&problem, false);
     RCP<Teuchos::ParameterList> pl = rcp(&belosList, false);
+    RCP<Belos::B200ResidualHistory<ST, MV, OP> > rec;
+    if (hist_rows) *hist_rows = 0;
     if (which == "BlockGmres") {
-      solver = rcp(new Belos::BlockGmresSolMgr<ST, MV, OP>(prob, pl));
+      RCP<Belos::BlockGmresSolMgr<ST, MV, OP> > bg = rcp(new Belos::BlockGmresSolMgr<ST, MV, OP>(prob, pl));
+      if (hist_cap_rows > 0 && hist) {
+        // setDebugStatusTest + setProblem: solve() rebuilds its status-test combo with the recorder in it
+        rec = rcp(new Belos::B200ResidualHistory<ST, MV, OP>());
+        bg->setDebugStatusTest(rec);
+        bg->setProblem(prob);
+      }
+      solver = bg;
     } else if (which == "PseudoBlockGmres") {
       belosList.remove("Adaptive Block Size");
       belosList.remove("Flexible Gmres", false);
@@ -144,6 +163,10 @@ extern "C" int b200_belos_solve_prec(const char* solver_name, b200_op* A_h, b200
     r->loss_of_accuracy = solver->isLOADetected() ? 1 : 0;
     r->solve_seconds = std::chrono::duration<double>(t1 - t0).count();
     r->num_rhs = numrhs;
+    if (nonnull(rec)) {
+      const int rows = rec->copy_out(hist, hist_cap_rows, numrhs);
+      if (hist_rows) *hist_rows = rows;
+    }
 
     // true residual check, as the reference driver does after solve()
     std::vector<double> actual(numrhs), rhs(numrhs);
@@ -155,8 +178,21 @@ extern "C" int b200_belos_solve_prec(const char* solver_name, b200_op* A_h, b200
     for (int i = 0; i < numrhs && i < 64; ++i)
       r->true_rel_resid[i] = rhs[i] > 0 ? actual[i] / rhs[i] : actual[i];
     return 0;
-  } catch (const std::exception& e) {
+  } catch (const Belos::B200MultiVecFailure& e) {
+    // a C-ABI call returned non-zero: hand its own status (CUDA, NCCL, timeout, shape ...) back
+    const int st = b200_last_status();
+    return b200::fail(st != 0 ? st : B200_ERR_ARG, e.what());
+  } catch (const Belos::B200OpFailure& e) {
+    const int st = b200_last_status();
+    return b200::fail(st != 0 ? st : B200_ERR_ARG, e.what());
+  } catch (const Belos::BelosError& e) {
+    // Belos' own failures (GmresIterationOrthoFailure rethrown by the manager, LinearProblemError,
+    // StatusTestError ...): BelosBlockGmresSolMgr.hpp:1161-1187
+    return b200::fail(B200_ERR_BELOS, e.what());
+  } catch (const std::invalid_argument& e) {
     return b200::fail(B200_ERR_ARG, e.what());
+  } catch (const std::exception& e) {
+    return b200::fail(B200_ERR_BELOS, e.what());
   }
 }
 

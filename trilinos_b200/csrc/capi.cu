@@ -399,12 +399,15 @@ extern "C" int b200_mv_trans_mv(const b200_mv* mv, double alpha, const b200_mv* 
       for (int i = 0; i < p; ++i) B[(size_t)j * ldb + i] = 0.0;
     return 0;
   }
-  if ((size_t)p * q > kMailboxDoubles)
+  // (the top of the mailbox, from kAuxBase, holds fused-epilogue results that pending memo entries point to)
+  if ((size_t)p * q > kAuxBase)
     return fail(B200_ERR_ARG, "MvTransMv: result block larger than the host mailbox");
   Ctx* ctx = mv->ctx;
   ++ctx->seq;
   ctx->plan_reduction(p * q, false);
-  for (int jv = 0; jv < q;) {
+  if (mv->n_local == 0)  // empty row block: this rank contributes zeros (and still joins the exchange)
+    B200_TRY(launch_zero_result(ctx, ctx->result_ptr(), p * q, ctx->make_pub(true)));
+  for (int jv = 0; jv < q && mv->n_local > 0;) {
     const int lv = run_length(jv, q, mv, jv);
     for (int ja = 0; ja < p;) {
       const int la = run_length(ja, p, A, ja);
@@ -473,6 +476,12 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
     jv += lv;
   }
   mv->touch(0, q);
+  if (fuse && mv->n_local == 0) {  // no kernel ran: the fused sums are zero, but must still be published
+    XchgPub pb;
+    pb.flag = fd.flag;
+    pb.seq = fd.seq;
+    B200_TRY(launch_zero_result(ctx, fd.out, 2 * q, pb));
+  }
   if (fuse) B200_TRY(fused_finish(ctx, fd, src, 2 * q));
   if (fuse)
     for (int j = 0; j < q; ++j) {
@@ -571,12 +580,13 @@ int halo_window_setup(Ctx* ctx, b200_op* op, size_t k) {
   int ok = ctx->p2p && op->peers.size() <= (size_t)kMaxPeers ? 1 : 0;
   for (const HaloPeer& pr : op->peers)
     if (pr.send_cnt <= 0 || pr.recv_cnt <= 0) ok = 0;
-  const size_t half = ((size_t)op->n_ghost * k * sizeof(double) + 255) / 256 * 256;
+  const size_t half = ((size_t)op->ghost_ld * k * sizeof(double) + 255) / 256 * 256;
   const size_t bytes = 256 + 2 * half;
   cudaIpcMemHandle_t mine;
   std::memset(&mine, 0, sizeof(mine));
   if (ok && cudaMalloc(&op->hwin, bytes) != cudaSuccess) ok = 0;
   if (ok && cudaMemset(op->hwin, 0, bytes) != cudaSuccess) ok = 0;
+  if (ok && cudaDeviceSynchronize() != cudaSuccess) ok = 0;  // zeroed before any peer can learn the handle
   if (ok && cudaIpcGetMemHandle(&mine, op->hwin) != cudaSuccess) ok = 0;
   cudaGetLastError();
   const size_t per = 9;
@@ -682,6 +692,7 @@ extern "C" int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_b
   op->row_end = re;
   op->n_local = n_local;
   op->n_ghost = n_ghost;
+  op->ghost_ld = ghost_pad(n_ghost);
   op->nnz = nnz;
   op->max_row_nnz = max_row;
   for (int i = 0; i < 3; ++i) {
@@ -692,6 +703,9 @@ extern "C" int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_b
     op->max_tile_nnz[i] = m;
   }
   op->n_bnd = (int64_t)bnd.size();
+  op->h_rowptr = rp;            // for the window plans of spmm_win.cu (built at the first apply)
+  op->h_colind = col_local;
+  op->h_values = vals;
   int rc = upload(&op->rowptr, rp);
   if (!rc) rc = upload(&op->colind, col_local);
   if (!rc) rc = upload(&op->values, vals);
@@ -726,6 +740,7 @@ extern "C" int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_b
       b200_op_destroy(op);
       return rc;
     }
+    for (int64_t v : M) op->any_halo = op->any_halo || v > 0;  // M is identical on every rank
     std::vector<int64_t> send_cnt(P, 0), send_off(P, 0);
     for (int r = 0; r < P; ++r) send_cnt[r] = M[(size_t)r * P + me];
     for (int r = 1; r < P; ++r) send_off[r] = send_off[r - 1] + send_cnt[r - 1];
@@ -778,6 +793,11 @@ extern "C" int b200_op_create_csr(b200_ctx* ctx, int64_t n_global, int64_t row_b
         op->peers.push_back(hp);
       }
   }
+  // the uploads above went through the legacy default stream; the kernels run on non-blocking streams
+  if (cudaDeviceSynchronize() != cudaSuccess) {
+    b200_op_destroy(op);
+    return fail(B200_ERR_CUDA, "b200_op_create_csr: device synchronisation failed");
+  }
   *out = op;
   return 0;
 }
@@ -792,6 +812,7 @@ extern "C" int b200_op_destroy(b200_op* op) {
   cudaFree(op->send_idx);
   cudaFree(op->send_buf);
   halo_window_release(op);  // (p2p: recv_buf pointed into the window and is reset here)
+  for (WinPlan& pl : op->win) free_win_plan(&pl);
   cudaFree(op->recv_buf);
   cudaFree(op->xcol);
   delete op;
@@ -834,12 +855,26 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
     const int len = run_length(j, k, x, j, y, j);
     const double* xp = x->col(j);
     double* yp = y->col(j);
-    if (ctx->nranks == 1 || op->peers.empty()) {
+    if (ctx->nranks == 1 || !op->any_halo) {
+      int wrc = 0;
+      const WinPlan* pl = win_plan_for(ctx, op, len, &wrc);
+      if (wrc) { rc = wrc; break; }
       FusedDots fd;
       size_t src = 0;
       const bool fuse = len == k && k <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src);
       ctx->t_begin(K_SPMM, algo_bytes * len / k);
-      rc = launch_spmm(ctx, op, nullptr, 0, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr);
+      if (pl) {  // x staged in shared memory (spmm_win.cu)
+        const int g = spmm_win_grid(ctx, *pl, len, pl->ntiles);
+        rc = launch_spmm_win(ctx, op, *pl, nullptr, pl->ntiles, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr, g,
+                             0, g, nullptr, nullptr);
+      } else if (op->n_local == 0 && fuse) {  // empty row block: the sums are zero, but must still be published
+        XchgPub pb;
+        pb.flag = fd.flag;
+        pb.seq = fd.seq;
+        rc = launch_zero_result(ctx, fd.out, k, pb);
+      } else {
+        rc = launch_spmm(ctx, op, nullptr, 0, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr);
+      }
       ctx->t_end();
       y->touch(j, len);
       if (fuse && !rc) rc = fused_finish(ctx, fd, src, k);
@@ -856,7 +891,7 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
         // peer-memory halo: put || interior rows -> boundary rows (which wait for the flags
         // themselves); no NCCL call
         const uint64_t hs = ++op->hseq;
-        const size_t half = ((size_t)op->n_ghost * op->buf_k * sizeof(double) + 255) / 256 * 256;
+        const size_t half = ((size_t)op->ghost_ld * op->buf_k * sizeof(double) + 255) / 256 * 256;
         const size_t par = (size_t)(hs & 1u);
         HaloPut hp;
         HaloWait hw;
@@ -865,12 +900,12 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
         hw.err = ctx->flag_d + 1;
         for (int pi = 0; pi < hp.npeers; ++pi) {
           const HaloPeer& pr = op->peers[pi];
-          const size_t rhalf = ((size_t)pr.remote_nghost * op->buf_k * sizeof(double) + 255) / 256 * 256;
+          const size_t rhalf = ((size_t)ghost_pad(pr.remote_nghost) * op->buf_k * sizeof(double) + 255) / 256 * 256;
           char* rw = static_cast<char*>(op->peer_hwin[pi]);
           hp.send_off[pi] = pr.send_off;
           hp.send_cnt[pi] = pr.send_cnt;
           hp.dst[pi] = reinterpret_cast<double*>(rw + 256 + par * rhalf) + pr.remote_off;
-          hp.dst_ld[pi] = pr.remote_nghost;
+          hp.dst_ld[pi] = ghost_pad(pr.remote_nghost);
           hp.flag[pi] = reinterpret_cast<uint64_t*>(rw) + ctx->rank;
           hw.flag[pi] = reinterpret_cast<const uint64_t*>(op->hwin) + pr.rank;
         }
@@ -886,13 +921,43 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
         rc = launch_halo_put(ctx, hp, op->send_idx, op->n_send, xp, x->ld, len, hs);
         if (rc) break;
         cudaEventRecord(ctx->ev_comm, ctx->comm_stream);
+        int wrc = 0;
+        const WinPlan* pl = win_plan_for(ctx, op, len, &wrc);
+        if (wrc) { rc = wrc; break; }
+        // every rank takes the fused y.y slot (the exchange behind it is collective), whichever
+        // kernel its own rows use
+        FusedDots fd;
+        size_t src = 0;
+        const bool fuse = len == k && k <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src);
         ctx->t_begin(K_SPMM, algo_bytes * len / k);
-        rc = launch_spmm(ctx, op, nullptr, -1, xp, x->ld, yp, y->ld, len);
-        if (!rc) rc = launch_spmm_boundary(ctx, op, hw, xp, x->ld, yp, y->ld, len);
+        if (pl) {
+          // interior tiles next to the put; boundary tiles (those with ghost runs) wait for the
+          // neighbours' flags themselves.  The y.y partials of both launches are folded by the last one.
+          const int64_t n1 = pl->n_int_tiles, n2 = pl->n_bnd_tiles;
+          const int g1 = n1 > 0 ? spmm_win_grid(ctx, *pl, len, n1) : 0;
+          const int g2 = n2 > 0 ? spmm_win_grid(ctx, *pl, len, n2) : 0;
+          if (n1 > 0)
+            rc = launch_spmm_win(ctx, op, *pl, pl->int_tiles_d, n1, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr,
+                                 g1 + g2, 0, n2 > 0 ? 0 : g1, nullptr, nullptr);
+          if (!rc && n2 > 0)
+            rc = launch_spmm_win(ctx, op, *pl, pl->bnd_tiles_d, n2, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr,
+                                 g1 + g2, g1, g1 + g2, &hw, nullptr);
+        } else {
+          rc = launch_spmm(ctx, op, nullptr, -1, xp, x->ld, yp, y->ld, len);
+          if (!rc) rc = launch_spmm_boundary(ctx, op, hw, xp, x->ld, yp, y->ld, len);
+          if (!rc && fuse) {
+            // gather kernels: no epilogue in the split apply -- one reduction launch into the fused slot
+            fd.flag = nullptr;
+            rc = launch_dot_into(ctx, yp, y->ld, op->n_local, len, fd.out);
+          }
+        }
         ctx->t_end();
         if (rc) break;
         cudaStreamWaitEvent(ctx->stream, ctx->ev_comm, 0);
         y->touch(j, len);
+        if (fuse) rc = fused_finish(ctx, fd, src, k);
+        if (fuse && !rc)
+          for (int c = 0; c < k; ++c) ctx->remember_dot(y->id(c), y->id(c), 0.0, fd.seq, src + c);
         j += len;
         continue;
       }
@@ -903,7 +968,7 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
         if (cudaMalloc((void**)&op->send_buf,
                        std::max<size_t>(1, (size_t)op->n_send * len) * 8) != cudaSuccess ||
             cudaMalloc((void**)&op->recv_buf,
-                       std::max<size_t>(1, (size_t)op->n_ghost * len) * 8) != cudaSuccess) {
+                       std::max<size_t>(1, (size_t)op->ghost_ld * len) * 8) != cudaSuccess) {
           rc = fail(B200_ERR_CUDA, "Apply: halo buffer allocation failed");
           break;
         }
@@ -929,7 +994,7 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
             rc = nccl_send(ctx, op->send_buf + (size_t)c * op->n_send + pr.send_off,
                            (size_t)pr.send_cnt, true, pr.rank, ctx->comm_stream);
           if (!rc && pr.recv_cnt > 0)
-            rc = nccl_recv(ctx, op->recv_buf + (size_t)c * op->n_ghost + pr.recv_off,
+            rc = nccl_recv(ctx, op->recv_buf + (size_t)c * op->ghost_ld + pr.recv_off,
                            (size_t)pr.recv_cnt, true, pr.rank, ctx->comm_stream);
         }
       }

@@ -307,44 +307,86 @@ __device__ __forceinline__ bool spin_acquire_sys(const uint64_t* flag, uint64_t 
 }
 
 
+// ---------------------------------------------------------------------------------------------
+// Low-latency peer exchange ("LL": value and sequence tag travel in the same store).
+// A double is sent as one 16-byte store {lo32, tag, hi32, tag}; each 8-byte half is written
+// atomically, so a reader that sees the expected tag in both halves has the whole value -- no
+// separate flag, no release fence waiting for the data to be acknowledged across NVLink, and the
+// receiver polls the data itself.  (The previous protocol -- data, CTA barrier, st.release.sys per
+// peer, acquire-spin on the flags -- paid one extra NVLink round trip per exchange.)
+struct __align__(16) LLWord { uint32_t lo, t0, hi, t1; };
+__device__ __forceinline__ void ll_store(LLWord* p, double v, uint32_t tag) {
+  const uint32_t lo = (uint32_t)__double2loint(v), hi = (uint32_t)__double2hiint(v);
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(lo), "r"(tag), "r"(hi), "r"(tag)
+               : "memory");
+}
+// false after ~30 s without the tag (a rank died or left the collective call sequence): the wait
+// gives up and records it in the host-visible error word instead of hanging the GPU
+__device__ __forceinline__ bool ll_load(const LLWord* p, uint32_t tag, double* out, uint64_t* err) {
+  uint32_t a, b, c, d, it = 0;
+  uint64_t t0 = 0;
+  while (true) {
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(p) : "memory");
+    if (b == tag && d == tag) break;
+    if ((++it & 0xfffu) == 0) {
+      uint64_t now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 30000000000ull) {
+        if (err) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(err), "l"((uint64_t)1) : "memory");
+        return false;
+      }
+    }
+  }
+  *out = __hiloint2double((int)c, (int)a);
+  return true;
+}
+
 // Hand a finished reduction to the host (see XchgPub in runtime.cuh).  Called by every thread of
 // the finishing CTA; results of this launch were stored by this CTA, those of earlier launches of
 // the same reduction by earlier kernels on the stream.
+//
+// nranks > 1: all-to-all LL exchange of this rank's partial result, fold in RANK ORDER (bitwise
+// identical on every rank, so the replicated host-side Belos state cannot diverge), result into the
+// host mailbox, then the host flag.  Window = [parity][source rank][kLL] LLWords; results longer than
+// kLL entries go in chunks, one exchange number (tag) per chunk.  A window half is re-used two
+// exchanges later; a peer can only be that far ahead after it has received this rank's contribution
+// to the exchange in between, which this rank sends after it finished reading (CTA barrier below).
 template <class Pub>
 __device__ __forceinline__ void publish_result(const Pub& pb) {
   if (pb.nranks <= 1) {
     publish_flag(pb.flag, pb.seq);
     return;
   }
-  constexpr int kFlagBytes = 512, kMaxR = 8, kSlot = 4096;  // kXchgFlagBytes, kMaxPeers, kXchgMax
+  constexpr int kMaxR = 8, kLL = 8192;  // kMaxPeers, kXchgMax
   __shared__ int timed_out;
   if (threadIdx.x == 0) timed_out = 0;
-  __syncthreads();
-  const int par = (int)(pb.xseq & 1u), P = pb.nranks, me = pb.rank;
-  for (int r = 0; r < P; ++r) {
-    double* slot = reinterpret_cast<double*>(static_cast<char*>(pb.win[r]) + kFlagBytes) +
-                   ((size_t)par * kMaxR + me) * kSlot;
-    for (int i = threadIdx.x; i < pb.count; i += blockDim.x) slot[i] = pb.src[i];
-  }
-  __syncthreads();
-  if ((int)threadIdx.x < P) {
-    uint64_t* pf = reinterpret_cast<uint64_t*>(static_cast<char*>(pb.win[threadIdx.x]) + par * 256) + me;
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pf), "l"(pb.xseq) : "memory");
-    const uint64_t* mf =
-        reinterpret_cast<const uint64_t*>(static_cast<char*>(pb.win[me]) + par * 256) + threadIdx.x;
-    if (!spin_acquire_sys(mf, pb.xseq, pb.err)) timed_out = 1;
-  }
-  __syncthreads();
-  if (timed_out) return;
-  const double* mine = reinterpret_cast<const double*>(static_cast<char*>(pb.win[me]) + kFlagBytes) +
-                       (size_t)par * kMaxR * kSlot;
-  for (int i = threadIdx.x; i < pb.count; i += blockDim.x) {
-    double t = __ldcg(mine + i);
-    for (int r = 1; r < P; ++r) {
-      const double v = __ldcg(mine + (size_t)r * kSlot + i);
-      t = pb.is_max ? fmax(t, v) : t + v;
+  __syncthreads();  // (also orders this CTA's result stores before the reads of pb.src below)
+  const int P = pb.nranks, me = pb.rank;
+  int ch = 0;
+  for (int c0 = 0; c0 < pb.count; c0 += kLL, ++ch) {
+    const uint64_t xs = pb.xseq + (uint64_t)ch;
+    const uint32_t tag = (uint32_t)xs;
+    const size_t half = (size_t)(xs & 1u) * kMaxR;
+    const int cnt = min(kLL, pb.count - c0);
+    for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+      const double v = pb.src[c0 + i];
+      for (int r = 0; r < P; ++r)
+        if (r != me) ll_store(static_cast<LLWord*>(pb.win[r]) + (half + me) * kLL + i, v, tag);
     }
-    pb.dst[i] = t;
+    const LLWord* mine = static_cast<const LLWord*>(pb.win[me]) + half * kLL;
+    for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+      double t = 0.0;
+      for (int r = 0; r < P; ++r) {
+        double v = 0.0;
+        if (r == me) v = pb.src[c0 + i];
+        else if (!ll_load(mine + (size_t)r * kLL + i, tag, &v, pb.err)) timed_out = 1;
+        t = r == 0 ? v : (pb.is_max ? fmax(t, v) : t + v);
+      }
+      pb.dst[c0 + i] = t;
+    }
+    __syncthreads();
+    if (timed_out) return;  // nothing is published: the host sees the error word
   }
   publish_flag(pb.flag, pb.seq);
 }

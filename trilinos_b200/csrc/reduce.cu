@@ -16,7 +16,7 @@ namespace b200 {
 namespace {
 
 // publish_result() (device_utils.cuh) restates the window layout
-static_assert(kXchgFlagBytes == 512 && kMaxPeers == 8 && kXchgMax == 4096, "window layout");
+static_assert(kMaxPeers == 8 && kXchgMax == 8192, "window layout");
 
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
@@ -109,6 +109,16 @@ int launch_dot(Ctx* ctx, const double* a, int64_t lda, const double* b, int64_t 
   return 0;
 }
 
+int launch_dot_into(Ctx* ctx, const double* a, int64_t lda, int64_t n, int k, double* out) {
+  if (k <= 0) return 0;
+  const dim3 g = red_grid(n, k);
+  const XchgPub pub;  // single-rank style with no flag: the finishing CTA only stores the sums
+  colreduce_kernel<RED_DOT_SELF><<<g, kThreads, 0, ctx->stream>>>(a, lda, nullptr, 0, n, ctx->ws, ctx->ticket, out, pub);
+  ++ctx->launches;
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int launch_norm(Ctx* ctx, const double* a, int64_t lda, int64_t n, int k, int type, int out_off,
                 bool last) {
   if (k <= 0) return 0;
@@ -145,59 +155,45 @@ __global__ void publish_kernel(const double* __restrict__ src, double* __restric
 }  // namespace
 
 namespace {
-// One CTA per rank.  (1) this rank's partial result -> slot [parity][me] of every rank's window
-// (own window included) over NVLink; (2) one release-store of the exchange number per peer flag;
-// (3) acquire-spin until every peer's flag for this exchange has arrived in the own window;
-// (4) fold the contributions in rank order -- the same order on every rank, so the replicated
-// host-side Belos state cannot diverge -- into the host mailbox and release the host flag.
-// A window half is re-used two exchanges later; a peer can only be that far ahead after it has seen
-// this rank's flag of the exchange in between, which this rank raises after it finished reading.
-template <bool IS_MAX>
-__global__ void __launch_bounds__(256)
-    xchg_publish_kernel(XchgWindow w, const double* __restrict__ src, double* __restrict__ dst,
-                        int count, uint64_t xseq, uint64_t* flag, uint64_t seq, uint64_t* err) {
-  __shared__ int timed_out;
-  if (threadIdx.x == 0) timed_out = 0;
-  const int par = (int)(xseq & 1u);
-  const int P = w.nranks, me = w.rank;
-  for (int r = 0; r < P; ++r) {
-    double* slot = reinterpret_cast<double*>(static_cast<char*>(w.win[r]) + kXchgFlagBytes) +
-                   ((size_t)par * kMaxPeers + me) * kXchgMax;
-    for (int i = threadIdx.x; i < count; i += blockDim.x) slot[i] = src[i];
-  }
-  __syncthreads();
-  if ((int)threadIdx.x < P) {
-    uint64_t* pf = reinterpret_cast<uint64_t*>(static_cast<char*>(w.win[threadIdx.x]) + par * 256) + me;
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pf), "l"(xseq) : "memory");
-    const uint64_t* mf = reinterpret_cast<const uint64_t*>(static_cast<char*>(w.win[me]) + par * 256) +
-                         threadIdx.x;
-    if (!spin_acquire_sys(mf, xseq, err)) timed_out = 1;
-  }
-  __syncthreads();
-  if (timed_out) return;  // nothing is published: the host sees the error word
-  const double* mine = reinterpret_cast<const double*>(static_cast<char*>(w.win[me]) + kXchgFlagBytes) +
-                       (size_t)par * kMaxPeers * kXchgMax;
-  for (int i = threadIdx.x; i < count; i += blockDim.x) {
-    double t = __ldcg(mine + i);
-    for (int r = 1; r < P; ++r) {
-      const double v = __ldcg(mine + (size_t)r * kXchgMax + i);
-      t = IS_MAX ? fmax(t, v) : t + v;
-    }
-    dst[i] = t;
-  }
-  publish_flag(flag, seq);
+// One CTA per rank: the peer exchange + rank-ordered fold + mailbox publish of publish_result()
+// (device_utils.cuh) as a kernel of its own -- for the results of fused reduction epilogues, which are
+// exchanged asynchronously behind the kernel that produced them.
+__global__ void __launch_bounds__(256) xchg_publish_kernel(const __grid_constant__ XchgPub pub) {
+  publish_result(pub);
 }
 }  // namespace
 
 int launch_xchg_publish(Ctx* ctx, const double* src_d, double* dst, int count, bool is_max,
                         uint64_t seq) {
-  ++ctx->xseq;
-  if (is_max)
-    xchg_publish_kernel<true><<<1, 256, 0, ctx->stream>>>(ctx->xw, src_d, dst, count, ctx->xseq,
-                                                         ctx->flag_d, seq, ctx->flag_d + 1);
-  else
-    xchg_publish_kernel<false><<<1, 256, 0, ctx->stream>>>(ctx->xw, src_d, dst, count, ctx->xseq,
-                                                          ctx->flag_d, seq, ctx->flag_d + 1);
+  XchgPub pb;
+  pb.flag = ctx->flag_d;
+  pb.seq = seq;
+  pb.nranks = ctx->nranks;
+  pb.rank = ctx->rank;
+  pb.count = count;
+  pb.is_max = is_max ? 1 : 0;
+  pb.xseq = ctx->xseq + 1;
+  ctx->xseq += (uint64_t)std::max(1, (count + kXchgMax - 1) / kXchgMax);
+  pb.src = src_d;
+  pb.dst = dst;
+  pb.err = ctx->flag_d + 1;
+  for (int i = 0; i < ctx->nranks; ++i) pb.win[i] = ctx->xw.win[i];
+  xchg_publish_kernel<<<1, 256, 0, ctx->stream>>>(pb);
+  ++ctx->launches;
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+namespace {
+__global__ void __launch_bounds__(256)
+    zero_result_kernel(double* __restrict__ out, int count, const __grid_constant__ XchgPub pub) {
+  for (int i = threadIdx.x; i < count; i += blockDim.x) out[i] = 0.0;
+  publish_result(pub);
+}
+}  // namespace
+
+int launch_zero_result(Ctx* ctx, double* out, int count, const XchgPub& pub) {
+  zero_result_kernel<<<1, 256, 0, ctx->stream>>>(out, count, pub);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
   return 0;

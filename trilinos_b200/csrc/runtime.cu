@@ -16,12 +16,15 @@
 namespace b200 {
 
 static thread_local char g_err[1024] = "";
+static thread_local int g_status = 0;
 
 int fail(int code, const char* msg) {
-  std::snprintf(g_err, sizeof(g_err), "%s", msg);
+  if (msg != g_err) std::snprintf(g_err, sizeof(g_err), "%s", msg);
+  g_status = code;
   return code;
 }
 int failf(int code, const char* fmt, ...) {
+  g_status = code;
   va_list ap;
   va_start(ap, fmt);
   std::vsnprintf(g_err, sizeof(g_err), fmt, ap);
@@ -215,6 +218,10 @@ int Ctx::wait_flag(uint64_t s) {
     }
   }
   std::atomic_thread_fence(std::memory_order_acquire);
+  // a peer-memory wait that gave up earlier in the stream (halo or exchange) leaves the error word set:
+  // whatever was published after it was computed from stale data.  Sticky until the context is destroyed.
+  if (flag_h[1] != 0)
+    return fail(B200_ERR_TIMEOUT, "a peer GPU did not arrive at an exchange within 30 s");
   return 0;
 }
 
@@ -257,7 +264,7 @@ void Ctx::plan_reduction(int count, bool is_max) {
   }();
   xplan_count = count;
   xplan_max = is_max;
-  xplan_ok = on && nranks > 1 && p2p && count <= kXchgMax;
+  xplan_ok = on && nranks > 1 && p2p;
   xplan_done = false;
 }
 
@@ -275,7 +282,8 @@ XchgPub Ctx::make_pub(bool last) {
   pb.rank = rank;
   pb.count = xplan_count;
   pb.is_max = xplan_max ? 1 : 0;
-  pb.xseq = ++xseq;
+  pb.xseq = xseq + 1;   // one exchange number per chunk of kXchgMax entries
+  xseq += (uint64_t)std::max(1, (xplan_count + kXchgMax - 1) / kXchgMax);
   pb.src = red_d;
   pb.dst = mbox_d;
   pb.err = flag_d + 1;
@@ -288,7 +296,7 @@ int Ctx::finish_reduction(int count, bool is_max) {
   const bool done = xplan_done;
   xplan_ok = xplan_done = false;
   if (nranks > 1 && !done) {
-    if (p2p && count <= kXchgMax) {
+    if (p2p) {
       B200_TRY(launch_xchg_publish(this, red_d, mbox_d, count, is_max, seq));
     } else {
       B200_TRY(nccl_allreduce_f64(this, red_d, (size_t)count, is_max, stream));
@@ -304,6 +312,7 @@ int Ctx::finish_reduction(int count, bool is_max) {
 using namespace b200;
 
 extern "C" const char* b200_last_error(void) { return g_err; }
+extern "C" int b200_last_status(void) { return g_status; }
 extern "C" const char* b200_version(void) { return "trilinos_b200 0.1 (sm_100a)"; }
 
 extern "C" int b200_ctx_create(int device, b200_ctx** out) {
@@ -397,6 +406,7 @@ static int setup_peer_windows(b200_ctx* c) {
   std::memset(&mine, 0, sizeof(mine));
   if (ok && cudaMalloc(&c->xwin, kXchgBytes) != cudaSuccess) ok = 0;
   if (ok && cudaMemset(c->xwin, 0, kXchgBytes) != cudaSuccess) ok = 0;
+  if (ok && cudaDeviceSynchronize() != cudaSuccess) ok = 0;  // zeroed before any peer can learn the handle
   if (ok && cudaIpcGetMemHandle(&mine, c->xwin) != cudaSuccess) ok = 0;
   cudaGetLastError();
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");

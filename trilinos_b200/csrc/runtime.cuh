@@ -48,12 +48,11 @@ constexpr size_t kPackBytes = 1u << 20;        // the same block in DMMA fragmen
 
 struct NcclApi;  // dlopen'ed function table (runtime.cu)
 
-// peer-memory exchange windows (see Ctx::xw).  Window layout: flags[2][kMaxPeers] (uint64, one
-// 256-B block per parity) followed by data[2][kMaxPeers][kXchgMax] doubles.
+// peer-memory exchange windows (see Ctx::xw).  Window layout: [parity][source rank][kXchgMax] 16-byte
+// LL words (value + sequence tag in one store, device_utils.cuh publish_result).
 constexpr int kMaxPeers = 8;
-constexpr int kXchgMax = 4096;   // largest result (doubles) exchanged through the windows
-constexpr size_t kXchgFlagBytes = 2 * 256;
-constexpr size_t kXchgBytes = kXchgFlagBytes + (size_t)2 * kMaxPeers * kXchgMax * sizeof(double);
+constexpr int kXchgMax = 8192;   // entries per exchange; longer results travel in chunks
+constexpr size_t kXchgBytes = (size_t)2 * kMaxPeers * kXchgMax * 16;
 struct XchgWindow {
   void* win[kMaxPeers] = {};     // win[r]: rank r's window as mapped in this process
   int nranks = 1, rank = 0;
@@ -120,7 +119,7 @@ struct Ctx {
   // host mailbox.  Replaces ncclAllReduce + publish kernel (~30 us) by one ~6 us kernel.
   XchgWindow xw;
   void* xwin = nullptr;            // this rank's window (cudaMalloc, IPC-exported)
-  uint64_t xseq = 0;               // exchange counter (parity selects the window half)
+  uint64_t xseq = 0;               // exchange counter (parity selects the window half; low 32 bits = LL tag)
   bool p2p = false;
   // NCCL
   NcclApi* nccl = nullptr;
@@ -253,6 +252,35 @@ struct HaloWait {
   uint64_t* err = nullptr;   // host-visible error word (set when a neighbour never arrives)
 };
 
+// ---- window-staged SpMM (spmm_win.cu): per-tile descriptor and per-operator plan --------------
+struct WinTile {
+  int64_t blob_off;        // byte offset of the tile's blob in WinPlan::blob_d (128-B aligned)
+  int32_t row0, nrows;     // first local row, rows (<= R)
+  int32_t width;           // stored entries per row (sliced-ELL width of this tile)
+  int32_t nruns, wlen;     // x-window runs and their total length (elements per right-hand side)
+  int32_t ghost_mask;      // bit j: run j lies in the ghost block (run_start relative to it)
+  int32_t run_start[8];    // first column of the run (multiple of 16)
+  int32_t run_len[8];      // elements (multiple of 16)
+  int32_t run_off[8];      // offset of the run inside the window
+};
+struct WinPlan {
+  int R = 0;               // rows per tile (0: not built yet)
+  bool ok = false;         // false: the format does not apply to this matrix
+  int64_t ntiles = 0;
+  WinTile* tiles_d = nullptr;
+  unsigned char* blob_d = nullptr;
+  size_t blob_bytes = 0;
+  int32_t* int_tiles_d = nullptr;  // multi-rank: tiles without / with ghost runs
+  int32_t* bnd_tiles_d = nullptr;
+  int64_t n_int_tiles = 0, n_bnd_tiles = 0;
+  int blob_cap = 0;        // largest tile blob (bytes, multiple of 128)
+  int wcap = 0;            // largest window (elements, multiple of 16)
+  double pad_ratio = 1.0;  // stored entries / nonzeros
+};
+
+// leading dimension of the ghost block: padded so that every right-hand side starts 256-B aligned
+inline int64_t ghost_pad(int64_t n_ghost) { return (n_ghost + 31) & ~(int64_t)31; }
+
 struct Op {
   Ctx* ctx;
   int64_t n_global, row_begin, row_end, n_local, n_ghost, nnz;
@@ -266,6 +294,10 @@ struct Op {
   int64_t n_int = 0;
   // halo
   std::vector<HaloPeer> peers;
+  // true when ANY rank of the communicator has a halo neighbour: the apply path (and with it the
+  // collectives it runs) is chosen from this globally agreed flag, never from the per-rank peer list --
+  // a rank whose rows happen to be decoupled still walks through the same collective steps
+  bool any_halo = false;
   int32_t* send_idx = nullptr;  // local row ids to pack, grouped by peer
   int64_t n_send = 0;
   double* send_buf = nullptr;   // n_send x k  (layout [rhs][row] per peer)
@@ -279,6 +311,11 @@ struct Op {
   void* hwin = nullptr;                 // own window
   void* peer_hwin[kMaxPeers] = {};      // peers[i]'s window as mapped here
   uint64_t hseq = 0;                    // applies done through the window (parity = hseq & 1)
+  int64_t ghost_ld = 0;                 // ghost_pad(n_ghost)
+  // host copy of the local CSR (rows sorted by local column id) for the window plans, built lazily
+  std::vector<int32_t> h_rowptr, h_colind;
+  std::vector<double> h_values;
+  WinPlan win[2];                       // R = 256, 128
   int max_row_nnz = 0;
   // largest nonzero count of any tile of 64 / 128 / 256 consecutive rows (SpMM stage sizing)
   int64_t max_tile_nnz[3] = {0, 0, 0};
@@ -309,6 +346,8 @@ int launch_dot(Ctx*, const double* a, int64_t lda, const double* b, int64_t ldb,
                int out_off, bool last);
 int launch_norm(Ctx*, const double* a, int64_t lda, int64_t n, int k, int type, int out_off,
                 bool last);
+// out[j] = sum a(:,j)^2 into a device buffer, nothing published (per-rank partial of a fused slot)
+int launch_dot_into(Ctx*, const double* a, int64_t lda, int64_t n, int k, double* out);
 // gram.cu : C(p x q, ld=ldc) = alpha * A^T V into result_ptr()+out_off
 int launch_gram(Ctx*, const double* A, int64_t lda, int p, const double* V, int64_t ldv, int q,
                 int64_t n, double alpha, int out_off, int ldc, bool last);
@@ -328,6 +367,16 @@ int launch_halo_put(Ctx*, const HaloPut& h, const int32_t* send_idx, int64_t n_s
 // boundary rows after a peer-memory halo: the kernel waits for the neighbours' flags itself
 int launch_spmm_boundary(Ctx*, const Op* op, const HaloWait& w, const double* x, int64_t ldx,
                          double* y, int64_t ldy, int k);
+
+// spmm_win.cu
+const WinPlan* win_plan_for(Ctx*, Op* op, int k, int* rc);
+void free_win_plan(WinPlan* plan);
+int spmm_win_grid(Ctx*, const WinPlan& pl, int k, int64_t ntiles);
+int launch_spmm_win(Ctx*, const Op* op, const WinPlan& pl, const int32_t* tile_list, int64_t ntiles,
+                    const double* x, int64_t ldx, double* y, int64_t ldy, int k, const FusedDots* fused,
+                    int pstride, int part_base, int part_total, const HaloWait* wait, int* grid_out);
+// out[0..count) = 0 and hand over as a finished reduction (empty local row block)
+int launch_zero_result(Ctx*, double* out, int count, const XchgPub& pub);
 
 // the mailbox publish kernel used after a multi-rank allreduce
 int launch_publish(Ctx*, int count);

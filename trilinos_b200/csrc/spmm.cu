@@ -441,7 +441,7 @@ int launch_spmm(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, cons
                 int64_t ldx, double* y, int64_t ldy, int k, const FusedDots* fused) {
   const int skip = (rows == nullptr && nrows == -1) ? 1 : 0;
   const double* xg = op->recv_buf;
-  const int64_t ldg = op->n_ghost;  // ghost block is stored densely per right-hand side
+  const int64_t ldg = op->ghost_ld;  // ghost block: one padded column per right-hand side
   int k0 = 0;
   while (k0 < k) {
     const int rem = k - k0;
@@ -500,7 +500,7 @@ int launch_halo_put(Ctx* ctx, const HaloPut& h, const int32_t* send_idx, int64_t
 int launch_spmm_boundary(Ctx* ctx, const Op* op, const HaloWait& w, const double* x, int64_t ldx,
                          double* y, int64_t ldy, int k) {
   const double* xg = op->recv_buf;
-  const int64_t ldg = op->n_ghost;
+  const int64_t ldg = op->ghost_ld;
   for (int k0 = 0; k0 < k;) {
     const int rem = k - k0;
     const int step = rem >= 16 ? 16 : rem >= 8 ? 8 : rem >= 4 ? 4 : rem >= 2 ? 2 : 1;

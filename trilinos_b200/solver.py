@@ -48,14 +48,18 @@ def solver_lib():
         _slib.b200_belos_solve_prec.argtypes = [C.c_char_p, vp, vp, C.c_int, vp, vp, C.POINTER(GmresParams),
                                                 C.POINTER(GmresResult)]
         _slib.b200_belos_solve_prec.restype = C.c_int
+        _slib.b200_belos_solve_hist.argtypes = [C.c_char_p, vp, vp, C.c_int, vp, vp, C.POINTER(GmresParams),
+                                                C.POINTER(GmresResult), C.POINTER(C.c_double), C.c_int,
+                                                C.POINTER(C.c_int)]
+        _slib.b200_belos_solve_hist.restype = C.c_int
         _slib.b200_belos_mvop_test.argtypes = [vp, C.c_int, C.c_int, C.c_int]
         _slib.b200_belos_mvop_test.restype = C.c_int
         _slib.b200_belos_timer_summary.argtypes = [C.c_char_p, C.c_int]
     return _slib
 
 
-SOLVER_EXPORTED = ("b200_gmres_default_params", "b200_belos_block_gmres_solve", "b200_belos_solve", "b200_belos_solve_prec", "b200_belos_mvop_test",
-                   "b200_belos_timer_summary")
+SOLVER_EXPORTED = ("b200_gmres_default_params", "b200_belos_block_gmres_solve", "b200_belos_solve", "b200_belos_solve_prec",
+                   "b200_belos_solve_hist", "b200_belos_mvop_test", "b200_belos_timer_summary")
 
 
 class BlockGmresSolMgr:
@@ -74,15 +78,29 @@ class BlockGmresSolMgr:
                                   1 if show_timers else 0)
         self.result = None
 
-    def solve(self, X, B):
-        """X: initial guess in / solution out; B: right-hand sides.  Returns a dict."""
+    def solve(self, X, B, history=0):
+        """X: initial guess in / solution out; B: right-hand sides.  Returns a dict.  history > 0 (BlockGmres only):
+        additionally record the native residual norms before each of the first `history` block iterations
+        (b200_belos_solve_hist) under the key "native_resid_history" ([iteration][rhs])."""
         r = GmresResult()
-        rc = solver_lib().b200_belos_solve_prec(self.SOLVER, self.op._h, self.prec._h if self.prec is not None else None,
-                                                self.left, X._h, B._h, C.byref(self.params), C.byref(r))
+        prec = self.prec._h if self.prec is not None else None
+        hist = None
+        if history > 0:
+            k = B.GetNumberVecs()
+            hist = (C.c_double * (history * k))()
+            rows = C.c_int(0)
+            rc = solver_lib().b200_belos_solve_hist(self.SOLVER, self.op._h, prec, self.left, X._h, B._h,
+                                                    C.byref(self.params), C.byref(r), hist, history, C.byref(rows))
+        else:
+            rc = solver_lib().b200_belos_solve_prec(self.SOLVER, self.op._h, prec, self.left, X._h, B._h,
+                                                    C.byref(self.params), C.byref(r))
         check(rc)
         self.result = dict(converged=bool(r.converged), num_iters=r.num_iters, achieved_tol=r.achieved_tol,
                            loss_of_accuracy=bool(r.loss_of_accuracy), solve_seconds=r.solve_seconds,
                            true_rel_resid=[r.true_rel_resid[i] for i in range(min(r.num_rhs, 64))])
+        if hist is not None:
+            nrow = min(rows.value, history)
+            self.result["native_resid_history"] = [[hist[i * k + j] for j in range(k)] for i in range(nrow)]
         return self.result
 
     def getNumIters(self):
