@@ -155,6 +155,28 @@ class B200MultiVec : public MultiVec<double> {
     }
   }
 
+#ifdef HAVE_BELOS_TSQR
+  /// TSQR hooks (belos/src/BelosMultiVec.hpp:213-293): Cholesky QR of the block on the Gram / update kernels,
+  /// SVD of the small factor on the host (trilinos_b200/csrc/tsqr.cu)
+  void factorExplicit(MultiVec<double>& Q, Teuchos::SerialDenseMatrix<int, double>& R,
+                      const bool forceNonnegativeDiagonal = false) override {
+    B200MultiVec* q = dynamic_cast<B200MultiVec*>(&Q);
+    TEUCHOS_TEST_FOR_EXCEPTION(q == nullptr, B200MultiVecFailure,
+                               "Belos::B200MultiVec::factorExplicit: Q is not a Belos::B200MultiVec.");
+    const int b = GetNumberVecs();
+    TEUCHOS_TEST_FOR_EXCEPTION(R.numRows() < b || R.numCols() < b, std::invalid_argument,
+                               "Belos::B200MultiVec::factorExplicit: R is " << R.numRows() << " x " << R.numCols()
+                                                                             << " but the block has " << b << " columns.");
+    B200_MV_CHECK(b200_mv_factor_explicit(h_, q->h_, R.values(), R.stride(), forceNonnegativeDiagonal ? 1 : 0),
+                  "factorExplicit");
+  }
+  int revealRank(Teuchos::SerialDenseMatrix<int, double>& R, const double& tol) override {
+    int rank = 0;
+    B200_MV_CHECK(b200_mv_reveal_rank(h_, R.values(), R.stride(), tol, &rank), "revealRank");
+    return rank;
+  }
+#endif  // HAVE_BELOS_TSQR
+
   /// host transfer helpers for drivers (ExtractCopy / copy-in)
   void copyToHost(double* host, ptrdiff_t ldh) const {
     B200_MV_CHECK(b200_mv_copy_to_host(h_, host, ldh), "copyToHost");

@@ -77,6 +77,11 @@ int b200_ctx_counters(const b200_ctx* ctx, int64_t* launches, int64_t* syncs);
  * environment.  dot_hits (may be NULL) returns how many column products were served that way. */
 int b200_ctx_set_fusion(b200_ctx* ctx, int on);
 int b200_ctx_fusion_stats(const b200_ctx* ctx, int64_t* dot_hits);
+/* Launches that never happened: single-column CloneCopy calls whose copy was made by the update kernel on its way
+ * or was never needed (lazy copies), and single-column MvScale factors applied by the skinny Gram kernel that read
+ * the column next (deferred scales).  DGKS findBasis makes one of each per column
+ * (belos/src/BelosDGKSOrthoManager.hpp:1037, :1217-1222). */
+int b200_ctx_deferral_stats(const b200_ctx* ctx, int64_t* lazy_copies_saved, int64_t* scales_folded);
 /* per-kernel-class device timing (CUDA events on the compute stream).
  * classes: 0 spmm, 1 trans_mv, 2 times_mat_add_mv, 3 dot/norm, 4 axpby/scale/copy, 5 halo */
 #define B200_NUM_KCLASS 6
@@ -135,6 +140,18 @@ int b200_mv_random(b200_mv* mv);
 /* MvInit(alpha) = PutScalar                      Epetra_MultiVector.cpp:595-608 */
 int b200_mv_init(b200_mv* mv, double alpha);
 /* host <-> device transfer of the local rows (ExtractCopy / ctor from array) */
+/* TSQR hooks of Belos::MultiVec (belos/src/BelosMultiVec.hpp:213-293), SURVEY 8 f.3 -- what
+ * Belos::TsqrOrthoManagerImpl calls through MultiVecTraits<>::tsqr_adaptor_type
+ * (belos/src/BelosTsqrOrthoManagerImpl.hpp:1546-1550).
+ * factor_explicit: A = Q R with orthonormal Q (n x b, another multivector of the same map) and the b x b factor R
+ *   (column-major, leading dimension ldr; upper triangular with a positive diagonal unless A is numerically rank
+ *   deficient, in which case R = Q^T A is full and Q's trailing columns span a complement -- reveal_rank sorts that
+ *   out).  Cholesky QR on the Gram / update kernels (trilinos_b200/csrc/tsqr.cu); b <= 64.
+ * reveal_rank: SVD of R = U S V^T (host); *rank = number of singular values > tol * largest.  Full rank: Q and R
+ *   unchanged; otherwise Q := Q U, R := S V^T (BelosMultiVec.hpp:252-283). */
+int b200_mv_factor_explicit(const b200_mv* A, b200_mv* Q, double* R, int ldr, int force_nonnegative_diagonal);
+int b200_mv_reveal_rank(b200_mv* Q, double* R, int ldr, double tol, int* rank);
+
 int b200_mv_copy_to_host(const b200_mv* mv, double* host, int64_t ldh);
 int b200_mv_copy_from_host(b200_mv* mv, const double* host, int64_t ldh);
 /* raw device pointer of column j and the leading dimension (harness / tests) */

@@ -86,6 +86,18 @@ int b200_belos_solve_hist(const char* solver, b200_op* A, b200_cheby* prec, int 
  * on a B200MultiVec of n rows x ncols columns and a tridiagonal B200CrsOp. 0 = passed. */
 int b200_belos_mvop_test(b200_ctx* ctx, int n, int ncols, int verbose);
 
+/* The checks of the reference's orthogonalisation-manager test, Belos::Test::OrthoManagerTester::runTests
+ * (belos/src/BelosOrthoManagerTest.hpp:353-760: normalize / projectAndNormalize on random and -- when
+ * rank_revealing != 0 -- rank-deficient blocks; orthonormality, orthogonality against the projected bases and
+ * reconstruction of the input), restated in belos_solver.cpp (that header does not compile against
+ * Belos::MultiVec<double> in this reference version), on
+ * B200MultiVec blocks of n rows with the manager OrthoManagerFactory makes for `ortho`
+ * ("TSQR" | "DGKS" | "ICGS" | "IMGS" | "Simple"), as belos/epetra/test/OrthoManager/belos_orthomanager_epetra.cpp
+ * does for Epetra.  "TSQR" = Belos::TsqrOrthoManager on the factorExplicit / revealRank hooks of the plugin class
+ * (SURVEY 8 f.3).  *num_failed = failed checks (0 = all passed). */
+int b200_belos_ortho_test(b200_ctx* ctx, const char* ortho, int n, int ncols, int size_x1, int size_x2,
+                          int rank_revealing, int verbose, int* num_failed);
+
 /* Timer table of the last solve (Teuchos::TimeMonitor::summarize) written into buf. */
 int b200_belos_timer_summary(char* buf, int buflen);
 

@@ -348,3 +348,144 @@ def test_fused_apply_dots(ctx, name, dims, k):
     assert relerr(d, oracle.dot(yref, yref)) <= TOL
     op.Apply(X, Y)                                  # rewritten: ids change, values identical
     assert relerr(Y.MvNorm(tb.NORM_TWO), oracle.norm(yref, 1)) <= TOL
+
+
+# ---- deferred single-column MvScale / lazy single-column CloneCopy (capi.cu prep_read / prep_write) ----------------
+def test_findbasis_sequence_without_copy_and_scale_launches(ctx):
+    """The per-column call sequence of DGKS findBasis (BelosDGKSOrthoManager.hpp:1000-1225): CloneCopy of column j,
+    MvTransMv against the previous columns, MvTimesMatAddMv, the two MvDot, MvScale.  Values must equal the oracle's;
+    the copy is filled by the update kernel and the scale by the next skinny Gram -- no launch of their own."""
+    n, b = 20011, 4
+    x = rnd(n, b, 41)
+    X = tb.MultiVec.from_numpy(ctx, x)
+    ref = x.copy()
+    lz0, sc0 = ctx.deferral_stats()
+    l0, _ = ctx.counters()
+    for j in range(b):
+        Xj = X.CloneViewNonConst([j])
+        old = Xj.CloneCopy() if j > 0 else None
+        old_dot = Xj.MvDot(Xj)
+        assert relerr(old_dot, oracle.dot(ref[:, [j]], ref[:, [j]])) <= TOL
+        if j > 0:
+            prev = X.CloneView(list(range(j)))
+            prod = Xj.MvTransMv(1.0, prev)
+            assert relerr(prod, oracle.trans_mv(1.0, ref[:, :j], ref[:, [j]])) <= TOL
+            refold = ref[:, [j]].copy()
+            Xj.MvTimesMatAddMv(-1.0, prev, prod, 1.0)
+            ref[:, [j]] = oracle.times_mat_add_mv(-1.0, ref[:, :j], prod, 1.0, ref[:, [j]])
+            new_dot = Xj.MvDot(Xj)
+            assert relerr(new_dot, oracle.dot(ref[:, [j]], ref[:, [j]])) <= TOL
+            od = Xj.MvDot(old)
+            assert np.abs(od - oracle.dot(ref[:, [j]], refold)).max() <= TOL * np.sqrt(new_dot * old_dot).max()
+            assert np.array_equal(old.to_numpy(), refold), "the lazy copy must hold the column as it was"
+        else:
+            new_dot = old_dot
+        s = 1.0 / np.sqrt(new_dot[0])
+        Xj.MvScale(s)
+        ref[:, j] = ref[:, j] * s
+    l1, _ = ctx.counters()
+    lz1, sc1 = ctx.deferral_stats()
+    assert lz1 - lz0 == b - 1, "every CloneCopy of the sequence must have been served by the update kernel"
+    assert sc1 - sc0 == b - 1, "the scales of columns 0..b-2 must have been folded into the next skinny Gram"
+    assert np.array_equal(X.to_numpy(), ref) or relerr(X.to_numpy(), ref) <= TOL   # (reading flushes the last scale)
+    q = oracle.trans_mv(1.0, X.to_numpy(), X.to_numpy())
+    assert np.abs(q - np.eye(b)).max() <= 1e-12
+
+
+def test_deferred_scale_is_visible_to_every_reader(ctx):
+    n = 7001
+    a = rnd(n, 3, 51)
+    for reader in ("to_numpy", "norm", "dot", "addmv", "apply_view", "gram_block", "clonecopy", "setblock", "update_src",
+                   "scale_again", "device_overwrite"):
+        A = tb.MultiVec.from_numpy(ctx, a)
+        c1 = A.CloneViewNonConst([1])
+        c1.MvScale(-2.5)                       # deferred
+        want = a.copy()
+        want[:, 1] *= -2.5
+        if reader == "to_numpy":
+            got = A.to_numpy()
+        elif reader == "norm":
+            assert relerr(A.MvNorm(tb.NORM_ONE), oracle.norm(want, 0)) <= TOL
+            got = A.to_numpy()
+        elif reader == "dot":
+            B = tb.MultiVec.from_numpy(ctx, a)
+            assert relerr(A.MvDot(B), oracle.dot(want, a)) <= TOL
+            got = A.to_numpy()
+        elif reader == "addmv":
+            B = tb.MultiVec(ctx, n, 3)
+            B.MvAddMv(1.0, A, 0.0, A)
+            got = B.to_numpy()
+        elif reader == "apply_view":
+            n2, rp, ci, va = tb.galeri("Tridiag", n)
+            op = tb.CrsOperator(ctx, n, 0, n, rp, ci, va)
+            Y = tb.MultiVec(ctx, n, 3)
+            op.Apply(A, Y)
+            assert relerr(Y.to_numpy(), oracle.spmm(rp, ci.astype(np.int32), va, want)) <= TOL
+            got = A.to_numpy()
+        elif reader == "gram_block":
+            assert relerr(A.MvTransMv(1.0, A), oracle.trans_mv(1.0, want, want)) <= TOL
+            got = A.to_numpy()
+        elif reader == "clonecopy":
+            got = A.CloneCopy().to_numpy()
+            assert np.array_equal(A.CloneCopy([1]).to_numpy(), want[:, [1]])
+        elif reader == "setblock":
+            B = tb.MultiVec(ctx, n, 3)
+            B.SetBlock(A, [0, 1, 2])
+            got = B.to_numpy()
+        elif reader == "update_src":
+            V = tb.MultiVec.from_numpy(ctx, a[:, [0]])
+            bm = rnd(3, 1, 52)
+            V.MvTimesMatAddMv(1.0, A, bm, 0.0)
+            assert relerr(V.to_numpy(), want @ bm) <= TOL
+            got = A.to_numpy()
+        elif reader == "scale_again":
+            c1.MvScale(4.0)                    # a second factor while the first is pending
+            want[:, 1] *= 4.0
+            got = A.to_numpy()
+        else:
+            A.MvInit(3.0)                      # overwriting drops the pending factor
+            want[:] = 3.0
+            got = A.to_numpy()
+        assert np.array_equal(got, want), reader
+
+
+def test_lazy_copy_survives_every_write_to_its_source(ctx):
+    n = 6007
+    a, b = rnd(n, 2, 61), rnd(n, 2, 62)
+    for write in ("scale", "init", "addmv", "update", "update_beta0", "update_block", "set_numpy", "random", "apply",
+                  "setblock", "destroy_source", "none"):
+        A = tb.MultiVec.from_numpy(ctx, a)
+        B = tb.MultiVec.from_numpy(ctx, b)
+        src = A.CloneViewNonConst([1])
+        cp = src.CloneCopy()                   # lazy
+        if write == "scale":
+            src.MvScale(2.0)
+        elif write == "init":
+            A.MvInit(1.0)
+        elif write == "addmv":
+            A.MvAddMv(1.0, A, 1.0, B)
+        elif write == "update":
+            src.MvTimesMatAddMv(-1.0, B, rnd(2, 1, 63), 1.0)      # the save_old path
+        elif write == "update_beta0":
+            src.MvTimesMatAddMv(-1.0, B, rnd(2, 1, 63), 0.0)
+        elif write == "update_block":
+            A.MvTimesMatAddMv(-1.0, B, rnd(2, 2, 64), 1.0)
+        elif write == "set_numpy":
+            A.set_numpy(b)
+        elif write == "random":
+            A.MvRandom()
+        elif write == "apply":
+            n2, rp, ci, va = tb.galeri("Tridiag", n)
+            op = tb.CrsOperator(ctx, n, 0, n, rp, ci, va)
+            op.Apply(B, A)
+        elif write == "setblock":
+            A.SetBlock(B, [1, 0])
+        elif write == "destroy_source":
+            del src
+            del A
+        assert np.array_equal(cp.to_numpy(), a[:, [1]]), write
+        # and a second lazy copy, of the copy
+        cp2 = cp.CloneCopy()
+        cp.MvScale(0.5)
+        assert np.array_equal(cp2.to_numpy(), a[:, [1]]), write
+        assert np.array_equal(cp.to_numpy(), a[:, [1]] * 0.5), write

@@ -50,6 +50,7 @@ _SIGS = {
     "b200_ctx_counters": (C.c_int, [vp, P(c_i64), P(c_i64)]),
     "b200_ctx_set_fusion": (C.c_int, [vp, C.c_int]),
     "b200_ctx_fusion_stats": (C.c_int, [vp, P(c_i64)]),
+    "b200_ctx_deferral_stats": (C.c_int, [vp, P(c_i64), P(c_i64)]),
     "b200_ctx_timing_enable": (C.c_int, [vp, C.c_int]),
     "b200_ctx_timing_read": (C.c_int, [vp, P(c_dbl), P(c_i64), P(c_dbl), C.c_int]),
     "b200_ctx_stream": (vp, [vp]),
@@ -73,6 +74,8 @@ _SIGS = {
     "b200_mv_set_block": (C.c_int, [vp, vp, P(C.c_int), C.c_int]),
     "b200_mv_random": (C.c_int, [vp]),
     "b200_mv_init": (C.c_int, [vp, c_dbl]),
+    "b200_mv_factor_explicit": (C.c_int, [vp, vp, P(c_dbl), C.c_int, C.c_int]),
+    "b200_mv_reveal_rank": (C.c_int, [vp, P(c_dbl), C.c_int, c_dbl, P(C.c_int)]),
     "b200_mv_copy_to_host": (C.c_int, [vp, P(c_dbl), c_i64]),
     "b200_mv_copy_from_host": (C.c_int, [vp, P(c_dbl), c_i64]),
     "b200_mv_device_ptr": (C.c_int, [vp, C.c_int, P(vp), P(c_i64)]),

@@ -80,6 +80,12 @@ class Context:
         check(lib.b200_ctx_fusion_stats(self._h, C.byref(a)))
         return a.value
 
+    def deferral_stats(self):
+        """(lazy single-column copies never launched, single-column scales folded into the next skinny Gram)"""
+        a, b = c_i64(), c_i64()
+        check(lib.b200_ctx_deferral_stats(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def timing_enable(self, on=True):
         check(lib.b200_ctx_timing_enable(self._h, 1 if on else 0))
 
@@ -212,6 +218,21 @@ class MultiVec:
 
     def MvInit(self, alpha=0.0):
         check(lib.b200_mv_init(self._h, float(alpha)))
+
+    # --- TSQR hooks (Belos::MultiVec::factorExplicit / revealRank) --------------------
+    def factorExplicit(self, Q, force_nonnegative_diagonal=False):
+        """self = Q R; Q: multivector with as many columns.  Returns R (b x b)."""
+        b = self.GetNumberVecs()
+        R = np.zeros((b, b), order="F")
+        check(lib.b200_mv_factor_explicit(self._h, Q._h, _dptr(R), max(1, b), 1 if force_nonnegative_diagonal else 0))
+        return R
+
+    def revealRank(self, R, tol):
+        """self = the Q of factorExplicit, R its factor (modified in place when rank deficient).  Returns the rank."""
+        assert R.flags.f_contiguous
+        rank = C.c_int(0)
+        check(lib.b200_mv_reveal_rank(self._h, _dptr(R), max(1, R.shape[0]), float(tol), C.byref(rank)))
+        return rank.value
 
     # --- host transfer ---------------------------------------------------------------
     def to_numpy(self):

@@ -15,6 +15,7 @@
 #include "BelosPseudoBlockGmresSolMgr.hpp"
 #include "BelosLinearProblem.hpp"
 #include "BelosMVOPTester.hpp"
+#include "BelosOrthoManagerFactory.hpp"
 #include "BelosOutputManager.hpp"
 #include "Teuchos_ParameterList.hpp"
 #include "Teuchos_RCP.hpp"
@@ -236,5 +237,145 @@ extern "C" int b200_belos_mvop_test(b200_ctx* ctx, int n, int ncols, int verbose
     return 0;
   } catch (const std::exception& e) {
     return b200::fail(B200_ERR_ARG, e.what());
+  }
+}
+
+namespace {
+typedef Teuchos::SerialDenseMatrix<int, ST> DM;
+
+double fro(const DM& M) { return M.normFrobenius(); }
+
+// || X^T Y ||_F  and  || X^T X - I ||_F, as OrthoManager::orthogError / orthonormError measure them
+double orthog_err(const MV& X, const MV& Y) {
+  DM Z(MVT::GetNumberVecs(X), MVT::GetNumberVecs(Y));
+  MVT::MvTransMv(1.0, X, Y, Z);
+  return fro(Z);
+}
+double orthonorm_err(const MV& X) {
+  const int k = MVT::GetNumberVecs(X);
+  DM Z(k, k);
+  MVT::MvTransMv(1.0, X, X, Z);
+  for (int i = 0; i < k; ++i) Z(i, i) -= 1.0;
+  return fro(Z);
+}
+double max_col_norm(const MV& X) {
+  std::vector<double> nrm(MVT::GetNumberVecs(X));
+  MVT::MvNorm(X, nrm);
+  double m = 0.0;
+  for (double v : nrm) m = std::max(m, v);
+  return m;
+}
+}  // namespace
+
+// The checks of Belos::Test::OrthoManagerTester (belos/src/BelosOrthoManagerTest.hpp:353-760, testNormalize
+// :1135-1298, testProjectAndNormalizeNew :1300-1475), restated: that header does not compile against
+// Belos::MultiVec<double> in this reference version (it calls MultiVecTraits::HasConstantStride and a misspelt
+// Teuchos::randomSyncedmatrix), so the same quantities are measured here with the same bounds:
+//   normalize(S, B):                 rank, || S^T S - I ||, || S_in - S B || / || S_in ||
+//   projectAndNormalize(S, C, B, Q): the same plus || Q_i^T S || and || S_in - sum Q_i C_i - S B || / || S_in ||
+// on a random block and, for rank-revealing managers, on a block with a duplicated column and a zero column.
+extern "C" int b200_belos_ortho_test(b200_ctx* ctx, const char* ortho, int n, int ncols, int size_x1,
+                                     int size_x2, int rank_revealing, int verbose, int* num_failed) {
+  using Teuchos::RCP;
+  using Teuchos::rcp;
+  if (!ctx || !ortho || !num_failed || n <= 0 || ncols <= 0 || size_x1 <= 0 || size_x2 <= 0)
+    return b200::fail(B200_ERR_ARG, "ortho_test: bad arguments");
+  *num_failed = -1;
+  try {
+    RCP<Belos::OutputManager<ST> > om = rcp(new Belos::OutputManager<ST>(
+        Belos::Errors | (verbose ? (Belos::Warnings | Belos::Debug) : 0), rcp(&std::cerr, false)));
+    int rank = 0, nranks = 1;
+    b200_ctx_rank(ctx, &rank, &nranks);
+    int64_t rb, re;
+    b200_linear_partition(n, nranks, rank, &rb, &re);
+    RCP<MV> S = rcp(new Belos::B200MultiVec(ctx, re - rb, n, rb, ncols));
+    MVT::MvRandom(*S);
+    Belos::OrthoManagerFactory<ST, MV, OP> factory;
+    RCP<Belos::OrthoManager<ST, MV> > OM =
+        factory.makeOrthoManager(std::string(ortho), Teuchos::null, om, "Belos", Teuchos::null);
+    const double tol = 1e-12 * std::sqrt((double)n);  // ~ the tester's 100 * eps * sqrt(n) scale
+    int failed = 0;
+    std::ostream& os = std::cerr;
+    auto check = [&](const char* what, double got, double bound) {
+      const bool ok = got <= bound;  // (false for NaN)
+      if (!ok) ++failed;
+      if (verbose || !ok) os << "ortho_test[" << ortho << "] " << what << ": " << got << (ok ? " <= " : " > ") << bound << std::endl;
+    };
+    // orthonormal bases X1, X2 to project against (built with the manager under test, as the tester does)
+    RCP<MV> X1 = MVT::Clone(*S, size_x1), X2 = MVT::Clone(*S, size_x2);
+    MVT::MvRandom(*X1);
+    MVT::MvRandom(*X2);
+    {
+      int r1 = OM->normalize(*X1, Teuchos::null);
+      check("normalize(X1): rank deficit", (double)(size_x1 - r1), 0.0);
+      check("normalize(X1): || X1^T X1 - I ||", orthonorm_err(*X1), tol);
+      Teuchos::Array<RCP<DM> > C(1, Teuchos::null);
+      Teuchos::Array<RCP<const MV> > Q(1, X1);
+      int r2 = OM->projectAndNormalize(*X2, C, Teuchos::null, Q);
+      check("projectAndNormalize(X2 | X1): rank deficit", (double)(size_x2 - r2), 0.0);
+      check("|| X2^T X2 - I ||", orthonorm_err(*X2), tol);
+      check("|| X1^T X2 ||", orthog_err(*X1, *X2), tol);
+    }
+    for (int variant = 0; variant < (rank_revealing ? 2 : 1); ++variant) {
+      // variant 0: random full-rank block; variant 1: column 1 := column 0 (dependent) and the last column := 0
+      RCP<MV> Sin = MVT::CloneCopy(*S);
+      int expect_rank = ncols;
+      if (variant == 1 && ncols >= 3) {
+        std::vector<int> c0(1, 0), c1(1, 1), cl(1, ncols - 1);
+        RCP<const MV> s0 = MVT::CloneView(*Sin, c0);
+        MVT::SetBlock(*s0, c1, *Sin);
+        RCP<MV> sl = MVT::CloneViewNonConst(*Sin, cl);
+        MVT::MvInit(*sl, 0.0);
+        expect_rank = ncols - 2;
+      }
+      const double scale = std::max(max_col_norm(*Sin), 1e-300);
+      {  // normalize
+        RCP<MV> W = MVT::CloneCopy(*Sin);
+        RCP<DM> B = rcp(new DM(ncols, ncols));
+        const int r = OM->normalize(*W, B);
+        check(variant ? "normalize(deficient): |rank - expected|" : "normalize: |rank - expected|",
+              std::fabs((double)(r - expect_rank)), 0.0);
+        if (r == ncols) check("normalize: || S^T S - I ||", orthonorm_err(*W), tol);
+        else {
+          std::vector<int> lead(std::max(r, 1));
+          for (int i = 0; i < (int)lead.size(); ++i) lead[i] = i;
+          RCP<const MV> Wl = MVT::CloneView(*W, lead);
+          check("normalize(deficient): || S_r^T S_r - I ||", orthonorm_err(*Wl), tol);
+        }
+        RCP<MV> Rs = MVT::CloneCopy(*Sin);
+        MVT::MvTimesMatAddMv(-1.0, *W, *B, 1.0, *Rs);
+        check("normalize: || S_in - S B || / || S_in ||", max_col_norm(*Rs) / scale, 100 * tol);
+      }
+      {  // projectAndNormalize against {X1, X2}
+        RCP<MV> W = MVT::CloneCopy(*Sin);
+        RCP<DM> B = rcp(new DM(ncols, ncols));
+        Teuchos::Array<RCP<DM> > C(2);
+        C[0] = rcp(new DM(size_x1, ncols));
+        C[1] = rcp(new DM(size_x2, ncols));
+        Teuchos::Array<RCP<const MV> > Q(2);
+        Q[0] = X1;
+        Q[1] = X2;
+        const int r = OM->projectAndNormalize(*W, C, B, Q);
+        check("projectAndNormalize: |rank - expected|", std::fabs((double)(r - expect_rank)), 0.0);
+        std::vector<int> lead(std::max(r, 1));
+        for (int i = 0; i < (int)lead.size(); ++i) lead[i] = i;
+        RCP<const MV> Wl = MVT::CloneView(*W, lead);
+        check("projectAndNormalize: || S^T S - I ||", orthonorm_err(*Wl), tol);
+        check("projectAndNormalize: || X1^T S ||", orthog_err(*X1, *Wl), tol);
+        check("projectAndNormalize: || X2^T S ||", orthog_err(*X2, *Wl), tol);
+        RCP<MV> Rs = MVT::CloneCopy(*Sin);
+        MVT::MvTimesMatAddMv(-1.0, *X1, *C[0], 1.0, *Rs);
+        MVT::MvTimesMatAddMv(-1.0, *X2, *C[1], 1.0, *Rs);
+        MVT::MvTimesMatAddMv(-1.0, *W, *B, 1.0, *Rs);
+        check("projectAndNormalize: || S_in - X1 C1 - X2 C2 - S B || / || S_in ||", max_col_norm(*Rs) / scale, 100 * tol);
+      }
+    }
+    *num_failed = failed;
+    return 0;
+  } catch (const Belos::B200MultiVecFailure& e) {
+    const int st = b200_last_status();
+    return b200::fail(st != 0 ? st : B200_ERR_ARG, e.what());
+  } catch (const std::exception& e) {
+    return b200::fail(B200_ERR_BELOS, e.what());
   }
 }

@@ -43,7 +43,7 @@ int new_mv(Ctx* ctx, int64_t n_local, int64_t n_global, int64_t row_offset, int 
     delete m;
     return rc;
   }
-  m->st = std::make_shared<Storage>(ctx, (double*)p, bytes, ncols);
+  m->st = std::make_shared<Storage>(ctx, (double*)p, bytes, ncols, m->ld, n_local);
   m->cols.resize(ncols);
   std::iota(m->cols.begin(), m->cols.end(), 0);
   *out = m;
@@ -92,6 +92,86 @@ bool fused_slot(Ctx* ctx, FusedDots* fd, size_t* src) {
 int fused_finish(Ctx* ctx, const FusedDots& fd, size_t src, int count) {
   if (ctx->nranks == 1) return 0;
   return launch_xchg_publish(ctx, fd.out, ctx->mbox_d + src, count, false, fd.seq);
+}
+
+
+// ---- deferred single-column scales and lazy single-column copies (see Storage in runtime.cuh) ------------------
+// forget the pending-copy link of (st, c) without making the copy
+void lazy_unlink(Storage* st, int c) {
+  Storage::Lazy& lz = st->lazy[(size_t)c];
+  if (!lz.src) return;
+  auto& d = lz.src->deps[(size_t)lz.col];
+  for (size_t i = 0; i < d.size(); ++i)
+    if (d[i].first == st && d[i].second == c) {
+      d.erase(d.begin() + (long)i);
+      break;
+    }
+  lz.src.reset();
+  lz.col = -1;
+  --st->ctx->pending;
+}
+
+// make the copy now (the source still holds the data: whoever overwrites a source column calls
+// deps_materialize first)
+int lazy_materialize(Storage* st, int c) {
+  Storage::Lazy& lz = st->lazy[(size_t)c];
+  if (!lz.src) return 0;
+  const Storage* s = lz.src.get();
+  B200_TRY(launch_axpby(st->ctx, st->colptr(c), st->ld, s->colptr(lz.col), s->ld, nullptr, 0, st->n_local, 1, 1.0, 0.0));
+  lazy_unlink(st, c);
+  return 0;
+}
+
+int deps_materialize(Storage* st, int c) {
+  while (!st->deps[(size_t)c].empty()) {
+    const auto d = st->deps[(size_t)c].back();
+    B200_TRY(lazy_materialize(d.first, d.second));
+  }
+  return 0;
+}
+
+int scale_flush(Storage* st, int c) {
+  const double f = st->pscale[(size_t)c];
+  if (f == 1.0) return 0;
+  B200_TRY(launch_axpby(st->ctx, st->colptr(c), st->ld, st->colptr(c), st->ld, nullptr, 0, st->n_local, 1, f, 0.0));
+  st->pscale[(size_t)c] = 1.0;
+  --st->ctx->pending;
+  return 0;
+}
+
+// Before a kernel READS columns [j0, j0 + len) of m: the data must be there.  keep_scale: the caller folds pending
+// scale factors in itself (skinny Gram).
+int prep_read(const MV* m, int j0 = 0, int len = -1, bool keep_scale = false) {
+  if (m->ctx->pending == 0) return 0;
+  if (len < 0) len = m->ncols() - j0;
+  Storage* st = m->st.get();
+  for (int j = j0; j < j0 + len; ++j) {
+    const int c = m->cols[(size_t)j];
+    B200_TRY(lazy_materialize(st, c));
+    if (!keep_scale) B200_TRY(scale_flush(st, c));
+  }
+  return 0;
+}
+
+// Before a kernel WRITES columns [j0, j0 + len) of m.  overwrite: the kernel never reads their old contents.
+int prep_write(const MV* m, int j0, int len, bool overwrite) {
+  if (m->ctx->pending == 0) return 0;
+  Storage* st = m->st.get();
+  for (int j = j0; j < j0 + len; ++j) {
+    const int c = m->cols[(size_t)j];
+    B200_TRY(deps_materialize(st, c));
+    if (overwrite) {
+      lazy_unlink(st, c);
+      if (st->pscale[(size_t)c] != 1.0) {
+        st->pscale[(size_t)c] = 1.0;
+        --st->ctx->pending;
+      }
+    } else {
+      B200_TRY(lazy_materialize(st, c));
+      B200_TRY(scale_flush(st, c));
+    }
+  }
+  return 0;
 }
 
 // Park-Miller jump: seed * 16807^e mod (2^31-1)
@@ -168,6 +248,33 @@ extern "C" int b200_mv_clone_copy(const b200_mv* mv, const int* index, int ninde
   B200_TRY(check_index(mv, index, nindex, "CloneCopy"));
   b200_mv* c = nullptr;
   B200_TRY(new_mv(mv->ctx, mv->n_local, mv->n_global, mv->row_offset, nindex, &c));
+  if (nindex == 1 && mv->ctx->fuse && !mv->st->external && mv->n_local > 0) {
+    // one column (DGKS findBasis' oldMXj, BelosDGKSOrthoManager.hpp:1037): the copy is made only if somebody
+    // reads it or the source is about to change
+    Storage* src = mv->st.get();
+    const int sc = mv->cols[(size_t)index[0]];
+    int rc = lazy_materialize(src, sc);   // (a copy of a pending copy: make the first one real)
+    if (!rc) rc = scale_flush(src, sc);
+    if (rc) {
+      delete c;
+      return rc;
+    }
+    c->st->lazy[0].src = mv->st;
+    c->st->lazy[0].col = sc;
+    src->deps[(size_t)sc].push_back({c->st.get(), 0});
+    ++mv->ctx->pending;
+    c->copy_id(0, mv, index[0]);
+    *out = c;
+    return 0;
+  }
+  {
+    int rc = 0;
+    for (int i = 0; i < nindex && !rc; ++i) rc = prep_read(mv, index[i], 1);
+    if (rc) {
+      delete c;
+      return rc;
+    }
+  }
   // copy maximal runs of consecutive source columns
   int j = 0;
   while (j < nindex) {
@@ -195,6 +302,7 @@ extern "C" b200_ctx* b200_mv_ctx(const b200_mv* mv) {
 
 extern "C" int b200_mv_init(b200_mv* mv, double alpha) {
   if (!mv) return fail(B200_ERR_ARG, "MvInit: null multivector");
+  B200_TRY(prep_write(mv, 0, mv->ncols(), true));
   for (int j = 0; j < mv->ncols();) {
     const int len = run_length(j, mv->ncols(), mv, j);
     B200_TRY(launch_fill(mv->ctx, mv->col(j), mv->ld, mv->n_local, len, alpha));
@@ -207,6 +315,7 @@ extern "C" int b200_mv_init(b200_mv* mv, double alpha) {
 extern "C" int b200_mv_random(b200_mv* mv) {
   if (!mv) return fail(B200_ERR_ARG, "MvRandom: null multivector");
   Ctx* ctx = mv->ctx;
+  B200_TRY(prep_write(mv, 0, mv->ncols(), true));
   for (int j = 0; j < mv->ncols();) {
     const int len = run_length(j, mv->ncols(), mv, j);
     B200_TRY(launch_random(ctx, mv->col(j), mv->ld, mv->n_local, len, mv->row_offset,
@@ -229,6 +338,9 @@ extern "C" int b200_mv_add_mv(b200_mv* mv, double alpha, const b200_mv* A, doubl
   Ctx* ctx = mv->ctx;
   const int k = mv->ncols();
   const int64_t n = mv->n_local;
+  if (alpha != 0.0) B200_TRY(prep_read(A));
+  if (beta != 0.0) B200_TRY(prep_read(B));
+  B200_TRY(prep_write(mv, 0, k, false));
   // alpha == 0 / beta == 0 short-circuits must not read the dropped operand
   // (epetra/src/Epetra_MultiVector.cpp:1348-1355)
   for (int j = 0; j < k;) {
@@ -261,6 +373,19 @@ extern "C" int b200_mv_add_mv(b200_mv* mv, double alpha, const b200_mv* A, doubl
 extern "C" int b200_mv_scale(b200_mv* mv, double alpha) {
   if (!mv) return fail(B200_ERR_ARG, "MvScale: null multivector");
   if (alpha == 1.0) return 0;
+  if (mv->ncols() == 1 && mv->ctx->fuse && !mv->st->external && mv->n_local > 0) {
+    // one column (the normalisation at the end of every findBasis column, BelosDGKSOrthoManager.hpp:1217-1222):
+    // remember the factor; the skinny Gram that reads the column next applies it on the way, anything else
+    // triggers the scale launch first
+    Storage* st = mv->st.get();
+    const int c = mv->cols[0];
+    B200_TRY(prep_write(mv, 0, 1, false));  // (copies of the unscaled column are made now; an older factor is applied)
+    st->pscale[(size_t)c] = alpha;
+    ++mv->ctx->pending;
+    mv->touch(0, 1);
+    return 0;
+  }
+  B200_TRY(prep_write(mv, 0, mv->ncols(), false));
   for (int j = 0; j < mv->ncols();) {
     const int len = run_length(j, mv->ncols(), mv, j);
     B200_TRY(launch_axpby(mv->ctx, mv->col(j), mv->ld, mv->col(j), mv->ld, nullptr, 0,
@@ -277,6 +402,7 @@ extern "C" int b200_mv_scale_cols(b200_mv* mv, const double* alpha, int nalpha) 
     return failf(B200_ERR_ARG,
                  "MvScale: vector of scaling factors has length %d, multivector has %d columns",
                  nalpha, mv->ncols());
+  B200_TRY(prep_write(mv, 0, mv->ncols(), false));
   for (int j = 0; j < mv->ncols();) {
     const int len = run_length(j, mv->ncols(), mv, j);
     B200_TRY(launch_scale_cols(mv->ctx, mv->col(j), mv->ld, mv->n_local, len, alpha + j));
@@ -291,6 +417,8 @@ extern "C" int b200_mv_set_block(b200_mv* mv, const b200_mv* A, const int* index
   B200_TRY(check_index(mv, index, nindex, "SetBlock"));
   if (A->ncols() < nindex) return fail(B200_ERR_ARG, "SetBlock: A has fewer columns than index");
   if (!same_map(mv, A)) return fail(B200_ERR_SHAPE, "SetBlock: vector lengths differ");
+  B200_TRY(prep_read(A, 0, nindex));
+  for (int i = 0; i < nindex; ++i) B200_TRY(prep_write(mv, index[i], 1, mv->col(index[i]) != A->col(i)));
   int j = 0;
   while (j < nindex) {
     int len = 1;
@@ -330,6 +458,8 @@ extern "C" int b200_mv_dot(const b200_mv* mv, const b200_mv* A, double* b, int n
     ctx->dot_hits += k;
     return 0;
   }
+  B200_TRY(prep_read(mv));
+  B200_TRY(prep_read(A));
   ++ctx->seq;
   ctx->plan_reduction(k, false);
   for (int j = 0; j < k;) {
@@ -370,6 +500,7 @@ extern "C" int b200_mv_norm(const b200_mv* mv, int type, double* normvec, int nn
       return 0;
     }
   }
+  B200_TRY(prep_read(mv));
   ++ctx->seq;
   ctx->plan_reduction(k, type == B200_NORM_INF);
   for (int j = 0; j < k;) {
@@ -403,6 +534,25 @@ extern "C" int b200_mv_trans_mv(const b200_mv* mv, double alpha, const b200_mv* 
   if ((size_t)p * q > kAuxBase)
     return fail(B200_ERR_ARG, "MvTransMv: result block larger than the host mailbox");
   Ctx* ctx = mv->ctx;
+  // one vector against <= 8 columns (findBasis): the skinny kernel applies pending column scales itself and
+  // writes the scaled columns back -- the normalisation of the previous column costs no launch
+  double scales[9];
+  bool fold = false;
+  if (ctx->pending > 0 && gram_is_skinny(p, q) && run_length(0, p, A, 0) == p && mv->n_local > 0) {
+    B200_TRY(prep_read(A, 0, p, true));
+    B200_TRY(prep_read(mv, 0, 1, true));
+    for (int i = 0; i < p; ++i) {
+      scales[i] = A->st->pscale[(size_t)A->cols[(size_t)i]];
+      fold = fold || scales[i] != 1.0;
+    }
+    scales[p] = mv->st->pscale[(size_t)mv->cols[0]];
+    fold = fold || scales[p] != 1.0;
+    // (the scaled columns are written back: copies of the stored, unscaled data cannot be pending -- MvScale
+    // made them real before it deferred the factor)
+  } else {
+    B200_TRY(prep_read(A));
+    B200_TRY(prep_read(mv));
+  }
   ++ctx->seq;
   ctx->plan_reduction(p * q, false);
   if (mv->n_local == 0)  // empty row block: this rank contributes zeros (and still joins the exchange)
@@ -413,10 +563,21 @@ extern "C" int b200_mv_trans_mv(const b200_mv* mv, double alpha, const b200_mv* 
       const int la = run_length(ja, p, A, ja);
       const bool last = (jv + lv >= q) && (ja + la >= p);
       B200_TRY(launch_gram(ctx, A->col(ja), A->ld, la, mv->col(jv), mv->ld, lv, mv->n_local,
-                           alpha, ja + jv * p, p, last));
+                           alpha, ja + jv * p, p, last, fold ? scales : nullptr));
       ja += la;
     }
     jv += lv;
+  }
+  if (fold) {  // the kernel stored the scaled columns
+    for (int i = 0; i <= p; ++i) {
+      Storage* st = i < p ? A->st.get() : mv->st.get();
+      const int c = i < p ? A->cols[(size_t)i] : mv->cols[0];
+      if (st->pscale[(size_t)c] != 1.0) {
+        st->pscale[(size_t)c] = 1.0;
+        --ctx->pending;
+        ++ctx->scale_folded;
+      }
+    }
   }
   B200_TRY(ctx->finish_reduction(p * q, false));
   for (int j = 0; j < q; ++j)
@@ -441,6 +602,25 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
   }
   if (columns_overlap(mv, A))
     return fail(B200_ERR_ALIAS, "MvTimesMatAddMv: A and mv share columns (DGEMM forbids aliasing)");
+  B200_TRY(prep_read(A));
+  // One-column update whose target has exactly one pending lazy copy (findBasis: oldMXj): the kernel reads the old
+  // values anyway and stores them into the copy on its way -- the CloneCopy launch never happens.
+  double* save_old = nullptr;
+  std::pair<Storage*, int> saved{nullptr, 0};
+  if (ctx->pending > 0 && q == 1 && beta != 0.0 && mv->n_local > 0 && run_length(0, p, A, 0) == p) {
+    Storage* st = mv->st.get();
+    const int c = mv->cols[0];
+    B200_TRY(lazy_materialize(st, c));
+    B200_TRY(scale_flush(st, c));
+    if (st->deps[(size_t)c].size() == 1) {
+      saved = st->deps[(size_t)c][0];
+      save_old = saved.first->colptr(saved.second);
+    } else {
+      B200_TRY(deps_materialize(st, c));
+    }
+  } else {
+    B200_TRY(prep_write(mv, 0, q, beta == 0.0));
+  }
   const size_t bytes = (size_t)p * q * sizeof(double);
   if (bytes > kStageSlotBytes)
     return fail(B200_ERR_ARG, "MvTimesMatAddMv: dense block larger than the staging slot");
@@ -469,13 +649,17 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
       const int la = run_length(ja, p, A, ja);
       B200_TRY(launch_update(ctx, mv->col(jv), mv->ld, lv, A->col(ja), A->ld, la, mv->n_local,
                              ctx->dB + ja + (size_t)jv * p, p, alpha, first ? beta : 1.0,
-                             fuse ? &fd : nullptr));
+                             fuse ? &fd : nullptr, save_old));
       first = false;
       ja += la;
     }
     jv += lv;
   }
   mv->touch(0, q);
+  if (save_old) {  // the copy now holds the old column
+    lazy_unlink(saved.first, saved.second);
+    ++ctx->lazy_saved;
+  }
   if (fuse && mv->n_local == 0) {  // no kernel ran: the fused sums are zero, but must still be published
     XchgPub pb;
     pb.flag = fd.flag;
@@ -496,6 +680,7 @@ extern "C" int b200_mv_copy_to_host(const b200_mv* mv, double* host, int64_t ldh
   if (!mv || !host) return fail(B200_ERR_ARG, "copy_to_host: null argument");
   if (ldh < mv->n_local) return fail(B200_ERR_ARG, "copy_to_host: ldh < local length");
   Ctx* ctx = mv->ctx;
+  B200_TRY(prep_read(mv));
   if (mv->n_local > 0) {
     for (int j = 0; j < mv->ncols();) {
       const int len = run_length(j, mv->ncols(), mv, j);
@@ -514,6 +699,7 @@ extern "C" int b200_mv_copy_from_host(b200_mv* mv, const double* host, int64_t l
   if (!mv || !host) return fail(B200_ERR_ARG, "copy_from_host: null argument");
   if (ldh < mv->n_local) return fail(B200_ERR_ARG, "copy_from_host: ldh < local length");
   Ctx* ctx = mv->ctx;
+  B200_TRY(prep_write(mv, 0, mv->ncols(), true));
   if (mv->n_local > 0) {
     for (int j = 0; j < mv->ncols();) {
       const int len = run_length(j, mv->ncols(), mv, j);
@@ -531,6 +717,14 @@ extern "C" int b200_mv_copy_from_host(b200_mv* mv, const double* host, int64_t l
 
 extern "C" int b200_mv_device_ptr(const b200_mv* mv, int col, void** ptr, int64_t* ld) {
   if (!mv || col < 0 || col >= mv->ncols()) return fail(B200_ERR_ARG, "device_ptr: bad column");
+  if (mv->ctx->pending > 0) {  // the caller sees raw memory from now on: nothing of this storage may stay pending
+    Storage* st = mv->st.get();
+    for (int c = 0; c < (int)st->ver.size(); ++c) {
+      B200_TRY(deps_materialize(st, c));
+      B200_TRY(lazy_materialize(st, c));
+      B200_TRY(scale_flush(st, c));
+    }
+  }
   mv->st->external = true;  // the caller may write through the pointer: stop tracking contents
   if (ptr) *ptr = mv->col(col);
   if (ld) *ld = mv->ld;
@@ -842,6 +1036,8 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
     return fail(B200_ERR_SHAPE, "Apply: multivector map does not match the operator");
   const int k = x->ncols();
   if (k == 0) return 0;
+  B200_TRY(prep_read(x));
+  B200_TRY(prep_write(y, 0, k, !columns_overlap(x, y)));
   // X == Y: Epetra applies into a temporary (Epetra_CrsMatrix.cpp:3152); do the same
   b200_mv* xtmp = nullptr;
   if (columns_overlap(x, y)) {
@@ -1030,6 +1226,9 @@ extern "C" int b200_mv_multiply_elementwise(b200_mv* mv, double scalar_ab, const
     return fail(B200_ERR_SHAPE, "Multiply: vector lengths differ (Epetra Multiply: -2)");
   Ctx* ctx = mv->ctx;
   const int k = mv->ncols();
+  B200_TRY(prep_read(A));
+  B200_TRY(prep_read(B));
+  B200_TRY(prep_write(mv, 0, k, false));
   for (int j = 0; j < k;) {
     const int len = run_length(j, k, mv, j, B, j);
     B200_TRY(launch_ewise_mul(ctx, mv->col(j), mv->ld, A->col(0), B->col(j), B->ld, mv->n_local, len,
@@ -1141,6 +1340,8 @@ extern "C" int b200_cheby_apply(b200_cheby* c, const b200_mv* x, b200_mv* y) {
   Ctx* ctx = x->ctx;
   const int k = x->ncols();
   if (k == 0) return 0;
+  B200_TRY(prep_read(x));
+  B200_TRY(prep_write(y, 0, k, !columns_overlap(x, y)));
   // AztecOO-style aliasing (x and y the same memory): work on a copy of x, as :482-488
   b200_mv* xcopy = nullptr;
   if (columns_overlap(x, y)) {

@@ -211,11 +211,20 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1)
 // 3 such calls per config-2 iteration, each over a few L2-resident columns.  The TMA ring moves
 // boxes one column wide for them (2 KB per copy, ~18 us per call); here every thread simply has
 // all its 256-bit loads in flight at once (~5 us).
+// Pending column scale factors (deferred MvScale, capi.cu): applied on the fly and written back, so the
+// normalisation at the end of a findBasis column (BelosDGKSOrthoManager.hpp:1217-1222) costs no launch of its own.
+struct SkinnyScale {
+  double a[8];
+  double v;
+  int any;
+};
+
 template <int PMAX>
 __global__ void __launch_bounds__(256)
-    gram_skinny_kernel(const double* __restrict__ A, int64_t lda, int p, const double* __restrict__ v,
+    gram_skinny_kernel(const double* A, int64_t lda, int p, const double* v,
                        int64_t n, double alpha, double* __restrict__ ws, unsigned int* ticket,
-                       double* __restrict__ out, const __grid_constant__ XchgPub pub) {
+                       double* __restrict__ out, const __grid_constant__ XchgPub pub,
+                       const __grid_constant__ SkinnyScale sc) {
   constexpr int kW = 8;
   const int64_t nvec = (n + 3) >> 2;
   double acc[PMAX][2];
@@ -223,11 +232,29 @@ __global__ void __launch_bounds__(256)
   for (int j = 0; j < PMAX; ++j) acc[j][0] = acc[j][1] = 0.0;
   for (int64_t i = blockIdx.x * 256ll + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * 256) {
     const int64_t r = 4 * i;
-    double4v vb = ld_keep4(v + r);
-    double4v va[PMAX];
+    double4v vb, va[PMAX];
+    if (!sc.any) {
+      vb = ld_keep4(v + r);
 #pragma unroll
-    for (int j = 0; j < PMAX; ++j)
-      if (j < p) va[j] = ld_keep4(A + (size_t)j * lda + r);
+      for (int j = 0; j < PMAX; ++j)
+        if (j < p) va[j] = ld_keep4(A + (size_t)j * lda + r);
+    } else {
+      // (coherent loads: these columns are written below; every element is read and written by this thread only)
+      vb = ld_plain4(v + r);
+#pragma unroll
+      for (int j = 0; j < PMAX; ++j)
+        if (j < p) va[j] = ld_plain4(A + (size_t)j * lda + r);
+      if (sc.v != 1.0) {
+        vb.x *= sc.v; vb.y *= sc.v; vb.z *= sc.v; vb.w *= sc.v;
+        st_plain4(const_cast<double*>(v) + r, vb);
+      }
+#pragma unroll
+      for (int j = 0; j < PMAX; ++j)
+        if (j < p && sc.a[j] != 1.0) {
+          va[j].x *= sc.a[j]; va[j].y *= sc.a[j]; va[j].z *= sc.a[j]; va[j].w *= sc.a[j];
+          st_plain4(const_cast<double*>(A) + (size_t)j * lda + r, va[j]);
+        }
+    }
     const bool m1 = r + 1 < n, m2 = r + 2 < n, m3 = r + 3 < n;  // padding rows of the last vector
     if (!m3) {
       if (!m1) vb.y = 0.0;
@@ -528,11 +555,11 @@ int launch_gram_t(Ctx* ctx, const double* A, int64_t lda, int p, const double* V
   B200_TRY(make_tmap(&tmA, A, n, p, lda, R, wfull));
   B200_TRY(make_tmap(&tmV, V, n, q, ldv, R, q));
   const size_t smem = stage_bytes * g.nstage + 128;
-  static bool attr_set = false;  // per template instantiation
-  if (!attr_set) {
+  static unsigned attr_devs = 0;  // bit per device: the attribute is per device, not per process
+  if (!(attr_devs & (1u << (ctx->device & 31)))) {
     B200_CUDA(cudaFuncSetAttribute(gram_tma_kernel<Q, CPW, NW>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(216u << 10)));
-    attr_set = true;
+    attr_devs |= 1u << (ctx->device & 31);
   }
   gram_tma_kernel<Q, CPW, NW><<<grid, (NW + 1) * 32, smem, ctx->stream>>>(g, tmA, tmV);
   ++ctx->launches;
@@ -573,11 +600,11 @@ int launch_gram_dmma(Ctx* ctx, const double* A, int64_t lda, int p, const double
   B200_TRY(make_tmap(&tmA, A, n, p, lda, R, wfull));
   B200_TRY(make_tmap(&tmV, V, n, Q, ldv, R, Q));
   const size_t smem = (size_t)g.sub * v_bytes + a_bytes * g.nstage + 128;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned attr_devs = 0;  // bit per device: the attribute is per device, not per process
+  if (!(attr_devs & (1u << (ctx->device & 31)))) {
     B200_CUDA(cudaFuncSetAttribute(gram_dmma_kernel<NTQ>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)(208u << 10)));
-    attr_set = true;
+    attr_devs |= 1u << (ctx->device & 31);
   }
   gram_dmma_kernel<NTQ><<<grid, 13 * 32, smem, ctx->stream>>>(g, tmA, tmV);
   ++ctx->launches;
@@ -587,11 +614,20 @@ int launch_gram_dmma(Ctx* ctx, const double* A, int64_t lda, int p, const double
 
 template <int PMAX>
 int launch_gram_skinny(Ctx* ctx, const double* A, int64_t lda, int p, const double* v, int64_t n,
-                       double alpha, double* out, const XchgPub& pub) {
+                       double alpha, double* out, const XchgPub& pub, const double* scales) {
   const int64_t nvec = (n + 3) / 4;
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nvec + 511) / 512, ctx->num_sms * 4));
+  SkinnyScale sc;
+  sc.any = 0;
+  sc.v = 1.0;
+  for (int j = 0; j < 8; ++j) sc.a[j] = 1.0;
+  if (scales) {
+    for (int j = 0; j < p; ++j) sc.a[j] = scales[j];
+    sc.v = scales[p];
+    sc.any = 1;
+  }
   gram_skinny_kernel<PMAX><<<grid, 256, 0, ctx->stream>>>(A, lda, p, v, n, alpha, ctx->ws, ctx->ticket,
-                                                          out, pub);
+                                                          out, pub, sc);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
   return 0;
@@ -599,9 +635,21 @@ int launch_gram_skinny(Ctx* ctx, const double* A, int64_t lda, int p, const doub
 
 }  // namespace
 
+static bool skinny_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200_SKINNY");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
+bool gram_is_skinny(int p, int q) { return q == 1 && p >= 1 && p <= 8 && skinny_enabled(); }
+
 int launch_gram(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, int64_t ldv, int q,
-                int64_t n, double alpha, int out_off, int ldc, bool last) {
+                int64_t n, double alpha, int out_off, int ldc, bool last, const double* scales) {
   if (p <= 0 || q <= 0) return 0;
+  if (scales && !gram_is_skinny(p, q))
+    return fail(B200_ERR_ARG, "MvTransMv: pending column scales reached a kernel that cannot apply them (internal)");
   double* out = ctx->result_ptr() + out_off;
   ctx->t_begin(K_GRAM, 8.0 * n * ((double)p + q));
   // q <= 8 and q = 16 are one pass over A (Q = next supported width; unused accumulator columns
@@ -620,14 +668,10 @@ int launch_gram(Ctx* ctx, const double* A, int64_t lda, int p, const double* V, 
     const int rem = q - k0;
     const int step = rem >= 16 ? 16 : (rem > 8 && dmma_on ? 8 : rem);
     const XchgPub flag = ctx->make_pub(last && k0 + step >= q);
-    static const bool skinny_on = [] {
-      const char* e = getenv("B200_SKINNY");
-      return !(e && e[0] == '0');
-    }();
-    if (q == 1 && p <= 8 && skinny_on) {
-      if (p <= 2) rc = launch_gram_skinny<2>(ctx, A, lda, p, Vk, n, alpha, outk, flag);
-      else if (p <= 4) rc = launch_gram_skinny<4>(ctx, A, lda, p, Vk, n, alpha, outk, flag);
-      else rc = launch_gram_skinny<8>(ctx, A, lda, p, Vk, n, alpha, outk, flag);
+    if (gram_is_skinny(p, q)) {
+      if (p <= 2) rc = launch_gram_skinny<2>(ctx, A, lda, p, Vk, n, alpha, outk, flag, scales);
+      else if (p <= 4) rc = launch_gram_skinny<4>(ctx, A, lda, p, Vk, n, alpha, outk, flag, scales);
+      else rc = launch_gram_skinny<8>(ctx, A, lda, p, Vk, n, alpha, outk, flag, scales);
     } else if (step == 16 && dmma_on)
       rc = launch_gram_dmma<2>(ctx, A, lda, p, Vk, ldv, n, alpha, outk, ldc, flag);
     else if (step == 8 && dmma_on)

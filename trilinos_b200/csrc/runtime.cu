@@ -116,6 +116,25 @@ int nccl_recv(Ctx* ctx, void* buf, size_t count, bool f64, int peer, cudaStream_
   return 0;
 }
 
+// ------------------------------------------------------------------ storage
+Storage::~Storage() {
+  // copies that were never needed: forget them at their sources (no launch ever happened)
+  for (size_t c = 0; c < lazy.size(); ++c)
+    if (lazy[c].src) {
+      auto& d = lazy[c].src->deps[(size_t)lazy[c].col];
+      for (size_t i = 0; i < d.size(); ++i)
+        if (d[i].first == this && d[i].second == (int)c) {
+          d.erase(d.begin() + (long)i);
+          break;
+        }
+      --ctx->pending;
+      ++ctx->lazy_saved;
+    }
+  for (double f : pscale)
+    if (f != 1.0) --ctx->pending;
+  ctx->release(ptr, bytes);
+}
+
 // ------------------------------------------------------------------ pool
 int Ctx::alloc(size_t bytes, void** out) {
   bytes = (bytes + 511) & ~(size_t)511;
@@ -509,6 +528,13 @@ extern "C" int b200_ctx_set_fusion(b200_ctx* c, int on) {
 extern "C" int b200_ctx_fusion_stats(const b200_ctx* c, int64_t* dot_hits) {
   if (!c) return fail(B200_ERR_ARG, "null context");
   if (dot_hits) *dot_hits = c->dot_hits;
+  return 0;
+}
+
+extern "C" int b200_ctx_deferral_stats(const b200_ctx* c, int64_t* lazy_copies_saved, int64_t* scales_folded) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  if (lazy_copies_saved) *lazy_copies_saved = c->lazy_saved;
+  if (scales_folded) *scales_folded = c->scale_folded;
   return 0;
 }
 

@@ -140,6 +140,8 @@ struct Ctx {
   int aux_next = 0;
   bool fuse = true;           // B200_NO_FUSE=1 disables the fused epilogues and the dot memo
   int64_t dot_hits = 0;
+  int64_t pending = 0;        // deferred scales + lazy copies outstanding (0: the prep_* hooks return at once)
+  int64_t lazy_saved = 0, scale_folded = 0;  // launches that never happened (diagnostics)
   void remember_dot(uint64_t a, uint64_t b, double val, uint64_t seq = 0, size_t src = 0);
   // true (and *val set, waiting for the producing kernel if needed) if the product is known
   bool recall_dot(uint64_t a, uint64_t b, double* val, int* rc);
@@ -178,14 +180,34 @@ struct Storage {
   Ctx* ctx;
   double* ptr;
   size_t bytes;
+  int64_t ld = 0, n_local = 0;
   // content id per storage column: equal ids <=> bitwise equal columns.  Every kernel that
   // writes a column gives it a fresh id; pure copies propagate the source id.
   std::vector<uint64_t> ver;
   bool external = false;  // a raw device pointer was handed out: contents are no longer tracked
-  Storage(Ctx* c, double* p, size_t b, int ncols) : ctx(c), ptr(p), bytes(b), ver((size_t)std::max(ncols, 1)) {
+  // Launch-bound single-column work of DGKS findBasis (BelosDGKSOrthoManager.hpp:1037, :1217-1222), kept
+  // off the stream until something needs the data (capi.cu: prep_read / prep_write):
+  //  * deferred MvScale of one column: its logical content is pscale[c] x the stored data; the skinny Gram
+  //    that reads the column next folds the factor in and writes the scaled column back, any other reader
+  //    applies it with a scale launch first;
+  //  * lazy CloneCopy of one column: column c of this storage is a copy of src:col that was not made
+  //    yet.  The copy that findBasis takes of column j is only ever read by one MvDot, which the dot memo
+  //    answers; the one-column update that overwrites the source stores the old values into the copy
+  //    on its way (no launch), and a copy that is released unread is never made.
+  struct Lazy {
+    std::shared_ptr<Storage> src;
+    int col = -1;
+  };
+  std::vector<double> pscale;
+  std::vector<Lazy> lazy;
+  std::vector<std::vector<std::pair<Storage*, int>>> deps;  // pending lazy copies OF column c
+  Storage(Ctx* c, double* p, size_t b, int ncols, int64_t ld_, int64_t n_)
+      : ctx(c), ptr(p), bytes(b), ld(ld_), n_local(n_), ver((size_t)std::max(ncols, 1)),
+        pscale((size_t)std::max(ncols, 1), 1.0), lazy((size_t)std::max(ncols, 1)), deps((size_t)std::max(ncols, 1)) {
     for (auto& v : ver) v = c->next_id++;
   }
-  ~Storage() { ctx->release(ptr, bytes); }
+  ~Storage();
+  double* colptr(int c) const { return ptr + (size_t)c * ld; }
 };
 
 struct MV {
@@ -349,13 +371,17 @@ int launch_norm(Ctx*, const double* a, int64_t lda, int64_t n, int k, int type, 
 // out[j] = sum a(:,j)^2 into a device buffer, nothing published (per-rank partial of a fused slot)
 int launch_dot_into(Ctx*, const double* a, int64_t lda, int64_t n, int k, double* out);
 // gram.cu : C(p x q, ld=ldc) = alpha * A^T V into result_ptr()+out_off
+// scales (skinny path only, see gram_is_skinny): p + 1 pending column factors (A's columns, then V's) that the
+// kernel applies and writes back; nullptr: none
 int launch_gram(Ctx*, const double* A, int64_t lda, int p, const double* V, int64_t ldv, int q,
-                int64_t n, double alpha, int out_off, int ldc, bool last);
+                int64_t n, double alpha, int out_off, int ldc, bool last, const double* scales = nullptr);
+bool gram_is_skinny(int p, int q);
 // update.cu : V = alpha*A*B + beta*V with B (p x q, ld = p) already in ctx->dB + boff
 // fused != nullptr: also emit {sum new^2, sum new*old} per column into fused->out[2k], [2k+1]
+// save_old (q == 1, beta != 0 only): the kernel also stores V's old values there (a pending lazy copy of V)
 int launch_update(Ctx*, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
                   int64_t n, const double* dB, int ldb, double alpha, double beta,
-                  const FusedDots* fused = nullptr);
+                  const FusedDots* fused = nullptr, double* save_old = nullptr);
 // spmm.cu
 // fused != nullptr (single rank, stream kernel only): also emit sum y(:,k)^2 into fused->out[k]
 int launch_spmm(Ctx*, const Op* op, const int32_t* rows, int64_t nrows, const double* x,

@@ -39,6 +39,7 @@ struct SpmmGeom {
   int cap;          // nonzeros per stage (multiple of 4)
   int stage_bytes;  // (cap + kSlack) * 12 + (R + 4) * 4, rounded up to 128
   int nstage;
+  int chunk;        // consecutive tiles per deal (tiles are dealt to the CTAs round-robin in chunks)
 };
 
 // Persistent TMA-streamed CSR kernel.
@@ -76,9 +77,23 @@ __global__ void __launch_bounds__(kThreadsC + 32, 3)
   // immediates instead of generic loads; 16-B alignment is all the bulk copies need)
   unsigned char* const stage0 = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // Tiles are dealt to the CTAs round-robin in chunks of g.chunk consecutive tiles: the grid works inside one
+  // band of rows that sweeps through the matrix, so x entries shared by tiles of neighbouring grid planes are
+  // re-read out of L2 shortly after their first use instead of out of DRAM a kernel duration later (at >= 3M rows
+  // x no longer fits L2), while consecutive tiles of a chunk still share L1 lines.
+  // (g.chunk == 0: one contiguous, balanced range per CTA -- kept for long-row stencils, measured below.)
   const int64_t ntiles = (n_rows + R - 1) / R;
-  const int64_t t_begin = ntiles * blockIdx.x / gridDim.x;
-  const int64_t t_end = ntiles * (blockIdx.x + 1) / gridDim.x;
+  const int64_t C = g.chunk > 0 ? g.chunk : 1;
+  const int64_t nchunks = (ntiles + C - 1) / C;
+  const int64_t my_chunks = (int64_t)blockIdx.x < nchunks ? (nchunks - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+  const int64_t t_first = ntiles * blockIdx.x / gridDim.x;
+  int64_t nseq = my_chunks * C;  // tiles of this CTA
+  if (my_chunks > 0 && blockIdx.x + (my_chunks - 1) * gridDim.x == nchunks - 1) nseq -= nchunks * C - ntiles;
+  if (g.chunk == 0) nseq = ntiles * (blockIdx.x + 1) / gridDim.x - t_first;
+  const bool contiguous = g.chunk == 0;
+  auto tile_of = [&](int64_t i) {
+    return contiguous ? t_first + i : ((i / C) * gridDim.x + blockIdx.x) * C + (i % C);
+  };
   const uint32_t off_c = (uint32_t)(g.cap + kSlack) * 8u, off_rp = (uint32_t)(g.cap + kSlack) * 12u;
 
   if (threadIdx.x == 0) {
@@ -106,28 +121,28 @@ __global__ void __launch_bounds__(kThreadsC + 32, 3)
     // are covered by their owners' prefetches.
     constexpr int kPfDist = 4;
     const bool pf_ok = ((reinterpret_cast<uintptr_t>(x) | (uintptr_t)(ldx * 8)) & 15) == 0;
-    auto prefetch_x = [&](int64_t t) {
-      if (!pf_ok || t >= t_end) return;
-      const int64_t r0 = t * R;
+    auto prefetch_x = [&](int64_t i) {
+      if (!pf_ok || i >= nseq) return;
+      const int64_t r0 = tile_of(i) * R;
       const uint32_t bytes = (uint32_t)(min((int64_t)R, n_rows - r0) * 8) & ~15u;
       if (bytes == 0) return;
 #pragma unroll
       for (int k = 0; k < K; ++k) bulk_prefetch_l2(x + (size_t)k * ldx + r0, bytes);
     };
     if (lane == 0)
-      for (int d = 0; d < kPfDist; ++d) prefetch_x(t_begin + d);
-    for (int64_t tb = t_begin; tb < t_end; tb += 32) {
-      const int64_t t = tb + lane;
+      for (int d = 0; d < kPfDist; ++d) prefetch_x(d);
+    for (int64_t tb = 0; tb < nseq; tb += 32) {
+      const int64_t t = tb + lane < nseq ? tile_of(tb + lane) : 0;
       int32_t sb = 0, se = 0;
-      if (t < t_end) {
+      if (tb + lane < nseq) {
         sb = __ldg(rowptr + t * R);
         se = __ldg(rowptr + min((t + 1) * (int64_t)R, n_rows));
       }
-      const int nt = (int)min((int64_t)32, t_end - tb);
+      const int nt = (int)min((int64_t)32, nseq - tb);
       for (int i = 0; i < nt; ++i) {
         const int32_t b = __shfl_sync(0xffffffffu, sb, i), e = __shfl_sync(0xffffffffu, se, i);
         if (lane == 0) {
-          const int64_t r0 = (tb + i) * R;
+          const int64_t r0 = tile_of(tb + i) * R;
           prefetch_x(tb + i + kPfDist);
           const uint32_t rp_cnt = (uint32_t)min((int64_t)kRp, (n_rows + 1 - r0 + 3) & ~(int64_t)3);
           int32_t base = b;
@@ -166,8 +181,8 @@ __global__ void __launch_bounds__(kThreadsC + 32, 3)
     double* yk = y + (size_t)(kgrp * KT) * ldy;
     int s = 0;
     uint32_t ph = 0;
-    for (int64_t tile = t_begin; tile < t_end; ++tile) {
-      const int64_t r0 = tile * R;
+    for (int64_t seq = 0; seq < nseq; ++seq) {
+      const int64_t r0 = tile_of(seq) * R;
       const int64_t r = r0 + row_t;
       const int nr = (int)min((int64_t)R, n_rows - r0);
       double acc[KT];
@@ -336,6 +351,7 @@ SpmmGeom spmm_geom(const Op* op, int R, int* ctas_per_sm) {
   nst = std::max(2, std::min(nst, kMaxStagesSpmm));
   if (force_stages >= 2) nst = std::min(nst, force_stages);
   g.nstage = nst;
+  g.chunk = 1;
   *ctas_per_sm = ctas;
   return g;
 }
@@ -375,17 +391,27 @@ int spmm_stream(Ctx* ctx, const Op* op, const double* x, int64_t ldx, const doub
   constexpr int R = kThreadsC / T;
   const int64_t ntiles = (op->n_local + R - 1) / R;
   if (ntiles == 0) return 0;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned attr_devs = 0;  // bit per device: the attribute is per device, not per process
+  if (!(attr_devs & (1u << (ctx->device & 31)))) {
     B200_CUDA(cudaFuncSetAttribute(spmm_stream_kernel<K, T, MODE>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)kSpmmSmemBudget + 128));
-    attr_set = true;
+    attr_devs |= 1u << (ctx->device & 31);
   }
   int ctas = 1;
-  const SpmmGeom g = spmm_geom(op, R, &ctas);
+  SpmmGeom g = spmm_geom(op, R, &ctas);
   const int smem = g.nstage * g.stage_bytes + 128;
   const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)ctx->num_sms * ctas);
+  // Measured (profiles/r2_sweep_s3.txt, cold L2): Laplace3D 200^3 k=4 300 -> 199 us and Recirc2D 2000^2 k=16
+  // 499 -> 353 us with single tiles dealt round-robin (x is then read from DRAM once instead of three times);
+  // Brick3D 150^3 k=8 (27 entries per row, 216 gathers per row: bound by the load pipe, not by DRAM) is fastest
+  // with the contiguous ranges of round 1 (377 us vs 391).  B200_SPMM_CHUNK overrides (0: contiguous).
+  static const int chunk_env = [] {
+    const char* e = getenv("B200_SPMM_CHUNK");
+    return e ? atoi(e) : -1;
+  }();
+  const double avg = op->n_local > 0 ? (double)op->nnz / (double)op->n_local : 0.0;
+  g.chunk = chunk_env >= 0 ? chunk_env : (avg > 12.0 ? 0 : 1);
   spmm_stream_kernel<K, T, MODE><<<grid, kThreadsC + 32, smem, ctx->stream>>>(
       op->rowptr, op->colind, op->values, op->n_local, (int32_t)op->n_local, x, ldx, xg, ldg, y,
       ldy, skip, g, fd);
@@ -524,7 +550,7 @@ int launch_spmm_boundary(Ctx* ctx, const Op* op, const HaloWait& w, const double
 int launch_pack(Ctx* ctx, cudaStream_t s, const int32_t* idx, int64_t cnt, const double* x,
                 int64_t ldx, int k, double* buf) {
   if (cnt <= 0 || k <= 0) return 0;
-  const unsigned bx = (unsigned)std::min<int64_t>((cnt + 255) / 256, kNumSM * 4);
+  const unsigned bx = (unsigned)std::min<int64_t>((cnt + 255) / 256, (int64_t)ctx->num_sms * 4);
   pack_kernel<<<dim3(bx, (unsigned)k), 256, 0, s>>>(idx, cnt, x, ldx, buf);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());

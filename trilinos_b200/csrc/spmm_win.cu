@@ -322,8 +322,12 @@ __global__ void __launch_bounds__(R + 32)
   unsigned char* const stage0p = smem_raw + (stage0 - smem_u32(smem_raw));
   const uint32_t stage_bytes = (uint32_t)a.blob_cap + (uint32_t)K * (uint32_t)a.wcap * 8u;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t t_begin = a.ntiles * blockIdx.x / gridDim.x;
-  const int64_t t_end = a.ntiles * (blockIdx.x + 1) / gridDim.x;
+  // Tiles are dealt ROUND-ROBIN: at any time the CTAs of the grid work inside one band of gridDim.x consecutive
+  // tiles that sweeps through the rows, so the three x planes a 7-point tile reads are fetched from DRAM once and
+  // served from L2 to the tiles of the neighbouring planes a few microseconds later.  (Contiguous tile ranges per
+  // CTA put the re-use a whole kernel duration apart: at 8M rows x no longer fits L2 and was read from DRAM three
+  // times -- 0.65 of the HBM roofline with the DRAM pipe saturated.)
+  const int64_t t_begin = blockIdx.x, t_end = a.ntiles, t_step = gridDim.x;
 
   if (threadIdx.x == 0) {
     give_up = 0;
@@ -354,14 +358,25 @@ __global__ void __launch_bounds__(R + 32)
     uint32_t ph = 0;
     const uint64_t pol_m = l2_policy_evict_first();  // the matrix is streamed once per apply
     const uint64_t pol_x = l2_policy_evict_last();   // x is re-read by the tiles of the neighbouring grid planes
-    for (int64_t t = t_begin; t < t_end; ++t) {
+    // The descriptor of tile t + 1 is fetched while tile t's copies are issued and its ring slot is awaited:
+    // a global-load round trip per tile on the producer's critical path left the consumers waiting for data.
+    struct Desc { int32_t width, nruns, wlen, gmask, rs, rl, ro; int64_t boff; };
+    const int l8 = lane & 7;
+    auto load_desc = [&](int64_t t) {
+      Desc d;
       const int64_t tid = a.tile_list ? (int64_t)__ldg(a.tile_list + t) : t;
       const WinTile* td = a.tiles + tid;
-      const int32_t width = __ldg(&td->width), nruns = __ldg(&td->nruns), wlen = __ldg(&td->wlen);
-      const int32_t gmask = __ldg(&td->ghost_mask);
-      const int64_t boff = __ldg(&td->blob_off);
-      const int l8 = lane & 7;
-      const int32_t rs = __ldg(&td->run_start[l8]), rl = __ldg(&td->run_len[l8]), ro = __ldg(&td->run_off[l8]);
+      d.width = __ldg(&td->width); d.nruns = __ldg(&td->nruns); d.wlen = __ldg(&td->wlen);
+      d.gmask = __ldg(&td->ghost_mask); d.boff = __ldg(&td->blob_off);
+      d.rs = __ldg(&td->run_start[l8]); d.rl = __ldg(&td->run_len[l8]); d.ro = __ldg(&td->run_off[l8]);
+      return d;
+    };
+    Desc nxt = load_desc(t_begin < t_end ? t_begin : 0);
+    for (int64_t t = t_begin; t < t_end; t += t_step) {
+      const Desc d = nxt;
+      if (t + t_step < t_end) nxt = load_desc(t + t_step);
+      const int32_t width = d.width, nruns = d.nruns, wlen = d.wlen, gmask = d.gmask, rs = d.rs, rl = d.rl, ro = d.ro;
+      const int64_t boff = d.boff;
       const uint32_t bbytes = ((uint32_t)kHdrBytes + (uint32_t)width * R * 10u + R + 127u) & ~127u;
       mbar_wait(&empty_bar[s], ph ^ 1u);
       unsigned char* st = stage0p + (size_t)s * stage_bytes;
@@ -390,7 +405,7 @@ __global__ void __launch_bounds__(R + 32)
     const int i = threadIdx.x;
     int s = 0;
     uint32_t ph = 0;
-    for (int64_t t = t_begin; t < t_end; ++t) {
+    for (int64_t t = t_begin; t < t_end; t += t_step) {
       mbar_wait(&full_bar[s], ph);
       const uint32_t st = stage0 + (uint32_t)s * stage_bytes;
       const int32_t row0 = lds_s32(st), nrows = lds_s32(st + 4), width = lds_s32(st + 8);
@@ -488,6 +503,11 @@ WinGeom win_geom(const WinPlan& pl, int K) {
   if (ctas < 1 || ctas * pl.R < 256) return g;
   int nst = (int)((kWinSmemBudget / ctas - 1280) / stage);
   nst = std::max(2, std::min(nst, kMaxStagesWin));
+  static const int force_st = [] {
+    const char* e = getenv("B200_WIN_STAGES");
+    return e ? atoi(e) : 0;
+  }();
+  if (force_st >= 2) nst = std::min(nst, force_st);
   g.ctas = ctas;
   g.nstage = nst;
   g.smem = (size_t)nst * stage + 128;
@@ -496,8 +516,8 @@ WinGeom win_geom(const WinPlan& pl, int K) {
 
 template <int K, int R>
 int win_launch_t(Ctx* ctx, const WinPlan& pl, const WinGeom& g, WinArgs& a, bool fuse, int grid) {
-  static int attr_dev_mask[2] = {0, 0};  // per device (bit) and per FUSE variant
-  const int bit = 1 << (ctx->device & 31);
+  static unsigned attr_dev_mask[2] = {0, 0};  // per device (bit) and per FUSE variant
+  const unsigned bit = 1u << (ctx->device & 31);
   if (!(attr_dev_mask[fuse ? 1 : 0] & bit)) {
     if (fuse)
       B200_CUDA(cudaFuncSetAttribute(spmm_win_kernel<K, R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -39,7 +39,7 @@ template <int Q, int UNR, bool FUSE>
 __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
     update_kernel(double* __restrict__ V, int64_t ldv, const double* __restrict__ A, int64_t lda,
                   int p, int64_t n, const double* __restrict__ B, int ldb, double alpha,
-                  double beta, FusedDots fd) {
+                  double beta, FusedDots fd, double* __restrict__ save_old) {
   __shared__ double Bs[kPChunk][Q];
   // Persistent CTAs (grid = resident capacity) walk the 512-row tiles round-robin: the fused
   // reduction's fence + ticket round trip (~2 us during which the CTA streams nothing) is paid
@@ -120,6 +120,8 @@ __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
           o.z = alpha * acc[2][k]; o.w = alpha * acc[3][k];
         } else {
           v = ld_plain4(vp);
+          // a pending lazy copy of this column (capi.cu, Q == 1 only) gets its data here
+          if (Q == 1 && save_old != nullptr) st_plain4(save_old + r, v);
           o.x = fma(alpha, acc[0][k], beta * v.x);
           o.y = fma(alpha, acc[1][k], beta * v.y);
           o.z = fma(alpha, acc[2][k], beta * v.z);
@@ -399,13 +401,13 @@ int launch_update_dmma(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_
   CUtensorMap tmA;
   B200_TRY(make_tmap(&tmA, A, n, p, lda, best, kUCB));
   const size_t smem = st_bytes * u.nstage + 128;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static unsigned attr_devs = 0;  // bit per device: the attribute is per device, not per process
+  if (!(attr_devs & (1u << (ctx->device & 31)))) {
     B200_CUDA(cudaFuncSetAttribute(update_dmma_kernel<NTQ, true>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(208u << 10)));
     B200_CUDA(cudaFuncSetAttribute(update_dmma_kernel<NTQ, false>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(208u << 10)));
-    attr_set = true;
+    attr_devs |= 1u << (ctx->device & 31);
   }
   if (fd.out)
     update_dmma_kernel<NTQ, true><<<grid, 13 * 32, smem, ctx->stream>>>(u, tmA);
@@ -419,9 +421,9 @@ int launch_update_dmma(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_
 template <int Q, int UNR>
 int launch_update_t(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_t lda, int p,
                     int64_t n, const double* dB, int ldb, double alpha, double beta,
-                    const FusedDots& fd) {
+                    const FusedDots& fd, double* save_old = nullptr) {
   const int64_t ntiles = (n + 4 * kThreads - 1) / (4 * kThreads);
-  static int per_sm = 0;  // resident CTAs per SM of this instantiation
+  static int per_sm = 0;  // resident CTAs per SM of this instantiation (a property of the kernel, same on every B200)
   if (per_sm == 0) {
     B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, update_kernel<Q, UNR, true>,
                                                             kThreads, 0));
@@ -430,10 +432,10 @@ int launch_update_t(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_t l
   const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)ctx->num_sms * per_sm);
   if (fd.out)
     update_kernel<Q, UNR, true><<<grid, kThreads, 0, ctx->stream>>>(V, ldv, A, lda, p, n, dB, ldb,
-                                                                     alpha, beta, fd);
+                                                                     alpha, beta, fd, save_old);
   else
     update_kernel<Q, UNR, false><<<grid, kThreads, 0, ctx->stream>>>(V, ldv, A, lda, p, n, dB,
-                                                                      ldb, alpha, beta, fd);
+                                                                      ldb, alpha, beta, fd, save_old);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
   return 0;
@@ -443,8 +445,10 @@ int launch_update_t(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_t l
 
 int launch_update(Ctx* ctx, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
                   int64_t n, const double* dB, int ldb, double alpha, double beta,
-                  const FusedDots* fused) {
+                  const FusedDots* fused, double* save_old) {
   if (n <= 0 || q <= 0) return 0;
+  if (save_old && (q != 1 || beta == 0.0))
+    return fail(B200_ERR_ARG, "MvTimesMatAddMv: save_old needs a one-column read-modify-write update (internal)");
   ctx->t_begin(K_UPDATE, 8.0 * n * ((double)p + (beta == 0.0 ? 1.0 : 2.0) * q));
   int k0 = 0, rc = 0;
   while (k0 < q && rc == 0) {
@@ -474,7 +478,7 @@ int launch_update(Ctx* ctx, double* V, int64_t ldv, int q, const double* A, int6
         rc = launch_update_t<8, 4>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
       case 4: rc = launch_update_t<4, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
       case 2: rc = launch_update_t<2, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
-      default: rc = launch_update_t<1, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
+      default: rc = launch_update_t<1, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd, save_old); break;
     }
     k0 += step;
   }

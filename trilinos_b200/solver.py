@@ -54,12 +54,15 @@ def solver_lib():
         _slib.b200_belos_solve_hist.restype = C.c_int
         _slib.b200_belos_mvop_test.argtypes = [vp, C.c_int, C.c_int, C.c_int]
         _slib.b200_belos_mvop_test.restype = C.c_int
+        _slib.b200_belos_ortho_test.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                                C.POINTER(C.c_int)]
+        _slib.b200_belos_ortho_test.restype = C.c_int
         _slib.b200_belos_timer_summary.argtypes = [C.c_char_p, C.c_int]
     return _slib
 
 
 SOLVER_EXPORTED = ("b200_gmres_default_params", "b200_belos_block_gmres_solve", "b200_belos_solve", "b200_belos_solve_prec",
-                   "b200_belos_solve_hist", "b200_belos_mvop_test", "b200_belos_timer_summary")
+                   "b200_belos_solve_hist", "b200_belos_mvop_test", "b200_belos_ortho_test", "b200_belos_timer_summary")
 
 
 class BlockGmresSolMgr:
@@ -145,3 +148,14 @@ def mvop_test(ctx, n=100, ncols=5, verbose=False):
     if rc != 0:
         raise B200Error(rc, lib.b200_last_error().decode(errors="replace"))
     return True
+
+
+def ortho_test(ctx, ortho="TSQR", n=500, ncols=12, size_x1=3, size_x2=5, rank_revealing=True, verbose=False):
+    """Belos::Test::OrthoManagerTester::runTests (belos/src/BelosOrthoManagerTest.hpp) on the B200 classes with the
+    orthogonalisation manager named `ortho`; returns the number of failed checks."""
+    nf = C.c_int(-1)
+    rc = solver_lib().b200_belos_ortho_test(ctx._h, ortho.encode(), n, ncols, size_x1, size_x2, 1 if rank_revealing else 0,
+                                            1 if verbose else 0, C.byref(nf))
+    if rc != 0:
+        raise B200Error(rc, lib.b200_last_error().decode(errors="replace"))
+    return nf.value
