@@ -62,12 +62,13 @@ bool columns_overlap(const MV* a, const MV* b) {
   return false;
 }
 
-// A mailbox slot + sequence number for a kernel with a fused reduction epilogue.  Single rank: the
-// kernel's last CTA publishes straight into the mailbox.  Multi-rank (peer windows available): the
-// kernel leaves this rank's partial sums in a device slot and fused_finish() queues the one-CTA
-// exchange kernel that folds all ranks' partials into the mailbox -- still without a host round
-// trip.  Remembered products that were still waiting in the recycled slot are dropped.
-bool fused_slot(Ctx* ctx, FusedDots* fd, size_t* src) {
+// A mailbox slot + sequence number for a kernel with a fused reduction epilogue of `count` results.  Single rank:
+// the kernel's last CTA publishes straight into the mailbox.  Multi-rank (peer windows available): the kernel
+// leaves this rank's partial sums in a device slot and its finishing CTA runs the peer exchange itself
+// (publish_result), folding all ranks' partials into the mailbox -- no host round trip, no exchange kernel.
+// The exchange numbers are taken here, i.e. in call order, which is the same on every rank.  Remembered
+// products that were still waiting in the recycled slot are dropped.
+bool fused_slot(Ctx* ctx, FusedDots* fd, size_t* src, int count) {
   if (!ctx->fuse || (ctx->nranks != 1 && !ctx->p2p)) return false;
   const int slot = ctx->aux_next;
   ctx->aux_next = (slot + 1) % kAuxSlots;
@@ -75,25 +76,36 @@ bool fused_slot(Ctx* ctx, FusedDots* fd, size_t* src) {
   for (int i = 0; i < kDotCache; ++i)
     if (ctx->dots[i].seq != 0 && ctx->dots[i].src >= base && ctx->dots[i].src < base + kAuxSlotDoubles)
       ctx->dots[i] = Ctx::DotEntry();
-  if (ctx->nranks == 1) {
-    fd->out = ctx->mbox_d + base;
-    fd->flag = ctx->flag_d;
-  } else {
-    fd->out = ctx->aux_d + (size_t)slot * kAuxSlotDoubles;
-    fd->flag = nullptr;
-  }
   fd->seq = ++ctx->seq;
   fd->ws = ctx->ws;
   fd->ticket = ctx->ticket;
+  fd->pub = XchgPub();
+  fd->pub.flag = ctx->flag_d;
+  fd->pub.seq = fd->seq;
+  if (ctx->nranks == 1) {
+    fd->out = ctx->mbox_d + base;
+  } else {
+    fd->out = ctx->aux_d + (size_t)slot * kAuxSlotDoubles;
+    fd->pub.nranks = ctx->nranks;
+    fd->pub.rank = ctx->rank;
+    fd->pub.count = count;
+    fd->pub.xseq = ctx->xseq + 1;
+    ctx->xseq += (uint64_t)std::max(1, (count + kXchgMax - 1) / kXchgMax);
+    fd->pub.src = fd->out;
+    fd->pub.dst = ctx->mbox_d + base;
+    fd->pub.err = ctx->flag_d + 1;
+    for (int i = 0; i < ctx->nranks; ++i) fd->pub.win[i] = ctx->xw.win[i];
+  }
   *src = base;
   return true;
 }
 
-int fused_finish(Ctx* ctx, const FusedDots& fd, size_t src, int count) {
+// For a fused slot whose sums were NOT produced by a kernel with the epilogue (a plain reduction launch filled the
+// slot): multi-rank, queue the one-CTA exchange kernel with the numbers fused_slot took.
+int fused_finish_separately(Ctx* ctx, const FusedDots& fd) {
   if (ctx->nranks == 1) return 0;
-  return launch_xchg_publish(ctx, fd.out, ctx->mbox_d + src, count, false, fd.seq);
+  return launch_xchg_pub(ctx, fd.pub);
 }
-
 
 // ---- deferred single-column scales and lazy single-column copies (see Storage in runtime.cuh) ------------------
 // forget the pending-copy link of (st, c) without making the copy
@@ -170,6 +182,24 @@ int prep_write(const MV* m, int j0, int len, bool overwrite) {
       B200_TRY(lazy_materialize(st, c));
       B200_TRY(scale_flush(st, c));
     }
+  }
+  return 0;
+}
+
+// Widest block of right-hand sides the window SpMM kernel takes in one launch for a `len`-wide apply (0: none;
+// *pl = its plan).  If the whole width does not fit the shared-memory window (16 right-hand sides of a 5-point
+// stencil), half or a quarter of it may: the matrix is then streamed once per group, which for short rows (the
+// matrix is a small share of the traffic) still beats the gather kernel (Recirc2D 2000^2: 0.85 vs 0.55 of the
+// HBM roofline at 8 vs 16 right-hand sides, profiles/r2_spmm_tile_dealing_sweep_s3.txt).
+int win_width(Ctx* ctx, Op* op, int len, const WinPlan** pl, int* rc) {
+  *pl = win_plan_for(ctx, op, len, rc);
+  if (*pl) return len;
+  if (*rc || op->n_local <= 0 || (double)op->nnz / (double)op->n_local > 8.0) return 0;
+  for (int kw = len / 2; kw >= 4; kw /= 2) {
+    if (len % kw) continue;
+    *pl = win_plan_for(ctx, op, kw, rc);
+    if (*rc) return 0;
+    if (*pl) return kw;
   }
   return 0;
 }
@@ -639,7 +669,7 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
   FusedDots fd;
   size_t src = 0;
   const bool fuse = run_length(0, p, A, 0) == p && run_length(0, q, mv, 0) == q &&
-                    2 * q <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src);
+                    2 * q <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src, 2 * q);
   std::vector<uint64_t> old_id(q);
   for (int j = 0; j < q; ++j) old_id[j] = mv->id(j);
   for (int jv = 0; jv < q;) {
@@ -660,13 +690,8 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
     lazy_unlink(saved.first, saved.second);
     ++ctx->lazy_saved;
   }
-  if (fuse && mv->n_local == 0) {  // no kernel ran: the fused sums are zero, but must still be published
-    XchgPub pb;
-    pb.flag = fd.flag;
-    pb.seq = fd.seq;
-    B200_TRY(launch_zero_result(ctx, fd.out, 2 * q, pb));
-  }
-  if (fuse) B200_TRY(fused_finish(ctx, fd, src, 2 * q));
+  if (fuse && mv->n_local == 0)  // no kernel ran: the fused sums are zero, but must still be handed over
+    B200_TRY(launch_zero_result(ctx, fd.out, 2 * q, fd.pub));
   if (fuse)
     for (int j = 0; j < q; ++j) {
       const uint64_t nid = mv->id(j);
@@ -1053,27 +1078,29 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
     double* yp = y->col(j);
     if (ctx->nranks == 1 || !op->any_halo) {
       int wrc = 0;
-      const WinPlan* pl = win_plan_for(ctx, op, len, &wrc);
+      const WinPlan* pl = nullptr;
+      const int kw = win_width(ctx, op, len, &pl, &wrc);
       if (wrc) { rc = wrc; break; }
       FusedDots fd;
       size_t src = 0;
-      const bool fuse = len == k && k <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src);
+      const bool fuse = len == k && k <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src, k);
       ctx->t_begin(K_SPMM, algo_bytes * len / k);
-      if (pl) {  // x staged in shared memory (spmm_win.cu)
-        const int g = spmm_win_grid(ctx, *pl, len, pl->ntiles);
-        rc = launch_spmm_win(ctx, op, *pl, nullptr, pl->ntiles, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr, g,
-                             0, g, nullptr, nullptr);
-      } else if (op->n_local == 0 && fuse) {  // empty row block: the sums are zero, but must still be published
-        XchgPub pb;
-        pb.flag = fd.flag;
-        pb.seq = fd.seq;
-        rc = launch_zero_result(ctx, fd.out, k, pb);
+      if (pl) {  // x staged in shared memory (spmm_win.cu), kw right-hand sides per launch
+        const int g = spmm_win_grid(ctx, *pl, kw, pl->ntiles);
+        for (int k0 = 0; k0 < len && !rc; k0 += kw) {
+          FusedDots f2 = fd;
+          f2.out = fd.out + k0;
+          if (k0 + kw < len) f2.not_last();  // the last group hands the results over
+          rc = launch_spmm_win(ctx, op, *pl, nullptr, pl->ntiles, xp + (size_t)k0 * x->ld, x->ld,
+                               yp + (size_t)k0 * y->ld, y->ld, kw, k0, fuse ? &f2 : nullptr, g, 0, g, nullptr, nullptr);
+        }
+      } else if (op->n_local == 0 && fuse) {  // empty row block: the sums are zero, but must still be handed over
+        rc = launch_zero_result(ctx, fd.out, k, fd.pub);
       } else {
         rc = launch_spmm(ctx, op, nullptr, 0, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr);
       }
       ctx->t_end();
       y->touch(j, len);
-      if (fuse && !rc) rc = fused_finish(ctx, fd, src, k);
       if (fuse && !rc)
         for (int c = 0; c < k; ++c) ctx->remember_dot(y->id(c), y->id(c), 0.0, fd.seq, src + c);
     } else {
@@ -1118,40 +1145,51 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
         if (rc) break;
         cudaEventRecord(ctx->ev_comm, ctx->comm_stream);
         int wrc = 0;
-        const WinPlan* pl = win_plan_for(ctx, op, len, &wrc);
+        const WinPlan* pl = nullptr;
+        const int kw = win_width(ctx, op, len, &pl, &wrc);
         if (wrc) { rc = wrc; break; }
         // every rank takes the fused y.y slot (the exchange behind it is collective), whichever
         // kernel its own rows use
         FusedDots fd;
         size_t src = 0;
-        const bool fuse = len == k && k <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src);
+        const bool fuse = len == k && k <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src, k);
         ctx->t_begin(K_SPMM, algo_bytes * len / k);
         if (pl) {
           // interior tiles next to the put; boundary tiles (those with ghost runs) wait for the
           // neighbours' flags themselves.  The y.y partials of both launches are folded by the last one.
+          // (kw right-hand sides per launch; every group has its own partial-sum region)
           const int64_t n1 = pl->n_int_tiles, n2 = pl->n_bnd_tiles;
-          const int g1 = n1 > 0 ? spmm_win_grid(ctx, *pl, len, n1) : 0;
-          const int g2 = n2 > 0 ? spmm_win_grid(ctx, *pl, len, n2) : 0;
-          if (n1 > 0)
-            rc = launch_spmm_win(ctx, op, *pl, pl->int_tiles_d, n1, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr,
-                                 g1 + g2, 0, n2 > 0 ? 0 : g1, nullptr, nullptr);
-          if (!rc && n2 > 0)
-            rc = launch_spmm_win(ctx, op, *pl, pl->bnd_tiles_d, n2, xp, x->ld, yp, y->ld, len, fuse ? &fd : nullptr,
-                                 g1 + g2, g1, g1 + g2, &hw, nullptr);
+          const int g1 = n1 > 0 ? spmm_win_grid(ctx, *pl, kw, n1) : 0;
+          const int g2 = n2 > 0 ? spmm_win_grid(ctx, *pl, kw, n2) : 0;
+          for (int pass = 0; pass < 2 && !rc; ++pass)
+            for (int k0 = 0; k0 < len && !rc; k0 += kw) {
+              FusedDots f2 = fd;
+              f2.out = fd.out + k0;
+              f2.ws = fd.ws + (size_t)k0 * (g1 + g2);
+              if (!(k0 + kw >= len && (pass == 1 || n2 == 0))) f2.not_last();  // the very last launch exchanges the slot
+              const double* xk = xp + (size_t)k0 * x->ld;
+              double* yk = yp + (size_t)k0 * y->ld;
+              if (pass == 0 && n1 > 0)
+                rc = launch_spmm_win(ctx, op, *pl, pl->int_tiles_d, n1, xk, x->ld, yk, y->ld, kw, k0,
+                                     fuse ? &f2 : nullptr, g1 + g2, 0, n2 > 0 ? 0 : g1, nullptr, nullptr);
+              if (pass == 1 && n2 > 0)
+                rc = launch_spmm_win(ctx, op, *pl, pl->bnd_tiles_d, n2, xk, x->ld, yk, y->ld, kw, k0,
+                                     fuse ? &f2 : nullptr, g1 + g2, g1, g1 + g2, &hw, nullptr);
+            }
         } else {
           rc = launch_spmm(ctx, op, nullptr, -1, xp, x->ld, yp, y->ld, len);
           if (!rc) rc = launch_spmm_boundary(ctx, op, hw, xp, x->ld, yp, y->ld, len);
           if (!rc && fuse) {
-            // gather kernels: no epilogue in the split apply -- one reduction launch into the fused slot
-            fd.flag = nullptr;
+            // gather kernels: no epilogue in the split apply -- one reduction launch into the fused slot, then
+            // the exchange as a kernel of its own
             rc = launch_dot_into(ctx, yp, y->ld, op->n_local, len, fd.out);
+            if (!rc) rc = fused_finish_separately(ctx, fd);
           }
         }
         ctx->t_end();
         if (rc) break;
         cudaStreamWaitEvent(ctx->stream, ctx->ev_comm, 0);
         y->touch(j, len);
-        if (fuse) rc = fused_finish(ctx, fd, src, k);
         if (fuse && !rc)
           for (int c = 0; c < k; ++c) ctx->remember_dot(y->id(c), y->id(c), 0.0, fd.seq, src + c);
         j += len;

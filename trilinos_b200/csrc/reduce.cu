@@ -178,6 +178,10 @@ int launch_xchg_publish(Ctx* ctx, const double* src_d, double* dst, int count, b
   pb.dst = dst;
   pb.err = ctx->flag_d + 1;
   for (int i = 0; i < ctx->nranks; ++i) pb.win[i] = ctx->xw.win[i];
+  return launch_xchg_pub(ctx, pb);
+}
+
+int launch_xchg_pub(Ctx* ctx, const XchgPub& pb) {
   xchg_publish_kernel<<<1, 256, 0, ctx->stream>>>(pb);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());

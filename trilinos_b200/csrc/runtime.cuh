@@ -76,11 +76,17 @@ struct XchgPub {
 
 // where a kernel with a fused reduction epilogue puts its column dot products
 struct FusedDots {
-  double* out = nullptr;        // device-visible mailbox slot (nullptr: no epilogue)
-  uint64_t* flag = nullptr;     // host flag, released with seq after the results are visible
+  double* out = nullptr;        // where the finishing CTA stores the sums (nullptr: no epilogue): the mailbox slot
+                                // (single rank) or this rank's partial-sum slot (multi-rank)
   uint64_t seq = 0;
   double* ws = nullptr;         // per-CTA partials
   unsigned int* ticket = nullptr;
+  // how the finishing CTA of the LAST launch of the operation hands the slot over: single rank -- release
+  // the host flag with seq; multi-rank -- the peer exchange of publish_result() (all `count` entries of the
+  // slot, rank-ordered fold into the mailbox) inside the producing kernel, so no exchange kernel is launched
+  // behind it.  Launches that are not the last one carry a default (inert) XchgPub.
+  XchgPub pub;
+  void not_last() { pub = XchgPub(); }
 };
 
 enum KClass { K_SPMM = 0, K_GRAM = 1, K_UPDATE = 2, K_REDUCE = 3, K_AXPBY = 4, K_HALO = 5 };
@@ -399,7 +405,7 @@ const WinPlan* win_plan_for(Ctx*, Op* op, int k, int* rc);
 void free_win_plan(WinPlan* plan);
 int spmm_win_grid(Ctx*, const WinPlan& pl, int k, int64_t ntiles);
 int launch_spmm_win(Ctx*, const Op* op, const WinPlan& pl, const int32_t* tile_list, int64_t ntiles,
-                    const double* x, int64_t ldx, double* y, int64_t ldy, int k, const FusedDots* fused,
+                    const double* x, int64_t ldx, double* y, int64_t ldy, int k, int k0, const FusedDots* fused,
                     int pstride, int part_base, int part_total, const HaloWait* wait, int* grid_out);
 // out[0..count) = 0 and hand over as a finished reduction (empty local row block)
 int launch_zero_result(Ctx*, double* out, int count, const XchgPub& pub);
@@ -409,6 +415,8 @@ int launch_publish(Ctx*, int count);
 // multi-rank with peer windows: exchange + fold + publish in one kernel (count <= kXchgMax)
 int launch_xchg_publish(Ctx*, const double* src_d, double* dst, int count, bool is_max,
                         uint64_t seq);
+// the same for an exchange that already has its numbers (XchgPub built by fused_slot / make_pub)
+int launch_xchg_pub(Ctx*, const XchgPub& pub);
 
 }  // namespace b200
 

@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(kThreadsC + 32, 3)
                        const double* __restrict__ values, int64_t n_rows, int32_t n_owned,
                        const double* __restrict__ x, int64_t ldx, const double* __restrict__ xg,
                        int64_t ldg, double* __restrict__ y, int64_t ldy, int skip_ghost_rows,
-                       SpmmGeom g, FusedDots fd) {
+                       SpmmGeom g, const __grid_constant__ FusedDots fd) {
   constexpr int R = kThreadsC / T;   // rows per tile
   constexpr int KT = K / T;          // right-hand sides per thread
   constexpr int U = KT >= 8 ? 2 : KT >= 4 ? 4 : 8;  // nonzeros per gather batch
@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(kThreadsC + 32, 3)
     fd.ws[(size_t)threadIdx.x * gridDim.x + blockIdx.x] = t;
   }
   if (!fold_partials_wide<kNWC + 1>(fd.ws, fd.ticket, K, gridDim.x, blockIdx.x, 1, fd.out)) return;
-  publish_flag(fd.flag, fd.seq);
+  publish_result(fd.pub);
 }
 
 // boundary rows (explicit list): one thread per row, direct loads
@@ -481,7 +481,7 @@ int launch_spmm(Ctx* ctx, const Op* op, const int32_t* rows, int64_t nrows, cons
     if (fused && fused->out && rows == nullptr && !skip && op->n_ghost == 0) {
       fd = *fused;
       fd.out = fused->out + k0;
-      if (k0 + step < k) fd.flag = nullptr;
+      if (k0 + step < k) fd.not_last();
     }
     if (rows != nullptr) {
       switch (step) {

@@ -483,7 +483,7 @@ __global__ void __launch_bounds__(R + 32)
     const double t = warp_sum(t0 + t1);
     if (lane == 0) a.fd.out[k] = t;
   }
-  publish_flag(a.fd.flag, a.fd.seq);
+  publish_result(a.fd.pub);
 }
 
 struct WinGeom { int ctas, nstage; size_t smem; };
@@ -572,8 +572,9 @@ const WinPlan* win_plan_for(Ctx* ctx, Op* op, int k, int* rc) {
 }
 
 // One launch of the window kernel over `ntiles` entries of tile_list (nullptr: all tiles).
+// (x, y: first of the k columns of this launch; k0: its index in the apply's block -- the ghost block holds all of them)
 int launch_spmm_win(Ctx* ctx, const Op* op, const WinPlan& pl, const int32_t* tile_list, int64_t ntiles,
-                    const double* x, int64_t ldx, double* y, int64_t ldy, int k, const FusedDots* fused,
+                    const double* x, int64_t ldx, double* y, int64_t ldy, int k, int k0, const FusedDots* fused,
                     int pstride, int part_base, int part_total, const HaloWait* wait, int* grid_out) {
   const WinGeom g = win_geom(pl, k);
   if (g.ctas <= 0) return fail(B200_ERR_ARG, "window SpMM: geometry does not fit (internal)");
@@ -586,7 +587,7 @@ int launch_spmm_win(Ctx* ctx, const Op* op, const WinPlan& pl, const int32_t* ti
   a.ntiles = ntiles;
   a.blob = pl.blob_d;
   a.x = x;
-  a.xg = op->recv_buf;
+  a.xg = op->recv_buf ? op->recv_buf + (size_t)k0 * op->ghost_ld : nullptr;
   a.y = y;
   a.ldx = ldx;
   a.ldg = op->ghost_ld;

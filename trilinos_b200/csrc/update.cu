@@ -39,7 +39,7 @@ template <int Q, int UNR, bool FUSE>
 __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
     update_kernel(double* __restrict__ V, int64_t ldv, const double* __restrict__ A, int64_t lda,
                   int p, int64_t n, const double* __restrict__ B, int ldb, double alpha,
-                  double beta, FusedDots fd, double* __restrict__ save_old) {
+                  double beta, const __grid_constant__ FusedDots fd, double* __restrict__ save_old) {
   __shared__ double Bs[kPChunk][Q];
   // Persistent CTAs (grid = resident capacity) walk the 512-row tiles round-robin: the fused
   // reduction's fence + ticket round trip (~2 us during which the CTA streams nothing) is paid
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
   }
   if (!fold_partials_wide<kThreads / 32>(fd.ws, fd.ticket, 2 * Q, gridDim.x, blockIdx.x, 1, fd.out))
     return;
-  publish_flag(fd.flag, fd.seq);
+  publish_result(fd.pub);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -211,7 +211,7 @@ __global__ void pack_b_kernel(const double* __restrict__ B, int ldb, int p, doub
 
 template <int NTQ, bool FUSE>
 __global__ void __launch_bounds__(13 * 32, 1)
-    update_dmma_kernel(const UpdArgs u, const __grid_constant__ CUtensorMap tmA) {
+    update_dmma_kernel(const __grid_constant__ UpdArgs u, const __grid_constant__ CUtensorMap tmA) {
   constexpr int NW = 12, Q = 8 * NTQ, PITCH = (Q == 8 ? 8 : 24);
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t full_bar[kUStages], empty_bar[kUStages];
@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(13 * 32, 1)
   }
   if (!fold_partials_wide<NW + 1>(u.fd.ws, u.fd.ticket, 2 * Q, gridDim.x, blockIdx.x, 1, u.fd.out))
     return;
-  publish_flag(u.fd.flag, u.fd.seq);
+  publish_result(u.fd.pub);
 }
 
 template <int NTQ>
@@ -466,7 +466,7 @@ int launch_update(Ctx* ctx, double* V, int64_t ldv, int q, const double* A, int6
     if (fused && fused->out) {
       fd = *fused;
       fd.out = fused->out + 2 * k0;
-      if (k0 + step < q) fd.flag = nullptr;  // only the last launch releases the sequence number
+      if (k0 + step < q) fd.not_last();  // only the last launch hands the results over
     }
     switch (step) {
       case 16: rc = launch_update_dmma<2>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
