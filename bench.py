@@ -107,6 +107,20 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+# The JSON line is the only thing this program writes to its stdout: file descriptor 1 is pointed at stderr for the
+# whole run (NCCL prints its version banner to stdout from C, torchrun's children inherit it) and emit() writes to
+# the saved descriptor.
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+sys.stdout.flush()
+os.dup2(2, 1)
+
+
+def emit(line):
+    _REAL_STDOUT.write(line + "\n")
+    _REAL_STDOUT.flush()
+
+
+
 def ref_threads():
     """Thread count of the reference arm: ALL PHYSICAL CORES of the host (one documented choice, the same in the
     reference arm and in cpu_baseline; a per-run timing probe moved the headline ratio by 25 % in round 1)."""
@@ -137,7 +151,7 @@ def reference_arm(args, wl):
     name, dims, b, m, ortho, tol, cfg = WORKLOADS[wl]
     if not ref.available():
         import oracle  # noqa: F401
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref was not built"}))
+        emit(json.dumps({"impl": "reference", "unavailable": "oracle/_ref was not built"}))
         return 0
     n, rp, ci, va = _ref_matrix(name, dims)
     xe, _ = ref.random(1, n, b)
@@ -162,7 +176,7 @@ def reference_arm(args, wl):
     val = iters / secs
     sample = (f"first restart cycle ({sample_iters} block iterations, basis width 0->{b * m}) of the {wl} solve, "
               f"Epetra OpenMP loops + OpenBLAS 0.3.15 on {cores} threads (all physical cores; {ref.max_threads()} logical)")
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * wall / max(args.steps, 1), "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -374,7 +388,7 @@ def main():
     perr, pok = parity_block(tb, ctx, rank, world)
     if not pok:
         if rank == 0:
-            print(json.dumps({"metric": METRIC, "parity_check": {"max_rel_err": perr, "ok": False}}))
+            emit(json.dumps({"metric": METRIC, "parity_check": {"max_rel_err": perr, "ok": False}}))
         raise SystemExit(f"parity block failed: max relative error {perr:.3e} (tolerance 1e-13)")
 
     w = Workload(tb, ctx, wl)
@@ -434,7 +448,7 @@ def main():
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(wl)
-        print(json.dumps(out))
+        emit(json.dumps(out))
     barrier()
     return 0
 

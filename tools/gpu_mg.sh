@@ -11,7 +11,7 @@ timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --ma
 tail -c 1500 gpurun_out/r2_bench_n$N.err
 python - <<PY
 import json
-d=json.load(open('gpurun_out/r2_bench_n$N.json'))
+d=json.loads([l for l in open('gpurun_out/r2_bench_n$N.json') if l.startswith('{')][-1])
 print('value',d['value'],'e2e',d['e2e']['value'],'launches',d['gpu_launches'],'syncs',d['host_syncs'], d['parity_check']['max_rel_err'])
 print({k:(v['calls'],v['frac']) for k,v in d['roofline']['kernels'].items()})
 for k in ('north_star_8m','c5_cycle'):

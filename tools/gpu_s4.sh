@@ -14,7 +14,7 @@ timeout 900 python bench.py --steps 5 --warmup 3 > gpurun_out/r2_bench_s4.json 2
 tail -c 2000 gpurun_out/r2_bench_s4.err
 python - <<'PY'
 import json
-d=json.load(open('gpurun_out/r2_bench_s4.json'))
+d=json.loads([l for l in open('gpurun_out/r2_bench_s4.json') if l.startswith('{')][-1])
 print('value',d['value'],'e2e',d['e2e']['value'],'launches',d['gpu_launches'],'syncs',d['host_syncs'])
 print({k:(v['calls'],v['frac']) for k,v in d['roofline']['kernels'].items()})
 for k in ('north_star_8m','c5_cycle'):
