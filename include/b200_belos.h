@@ -77,6 +77,13 @@ int b200_ctx_counters(const b200_ctx* ctx, int64_t* launches, int64_t* syncs);
  * environment.  dot_hits (may be NULL) returns how many column products were served that way. */
 int b200_ctx_set_fusion(b200_ctx* ctx, int on);
 int b200_ctx_fusion_stats(const b200_ctx* ctx, int64_t* dot_hits);
+/* Fused update + Gram: block Gram-Schmidt makes two passes, C = Q^T X; X -= Q C; C2 = Q^T X; X -= Q C2
+ * (belos/src/BelosDGKSOrthoManager.hpp:1400-1472).  When the call pattern predicts that MvTransMv(Q, X) follows an
+ * MvTimesMatAddMv(-1, Q, C, 1, X), the update kernel also accumulates Q^T X_new from the tile of Q it has staged and the
+ * MvTransMv is answered from the mailbox: one pass over Q of four disappears.  launches = updates that ran fused,
+ * hits = MvTransMv calls answered that way.  B200_SPEC_GRAM=0 in the environment disables it, =2 fuses every
+ * eligible update (p <= 256 basis columns, <= 8 right-hand sides). */
+int b200_ctx_spec_gram_stats(const b200_ctx* ctx, int64_t* launches, int64_t* hits);
 /* Launches that never happened: single-column CloneCopy calls whose copy was made by the update kernel on its way
  * or was never needed (lazy copies), and single-column MvScale factors applied by the skinny Gram kernel that read
  * the column next (deferred scales).  DGKS findBasis makes one of each per column

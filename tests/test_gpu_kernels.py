@@ -32,7 +32,8 @@ SIZES = [1, 3, 31, 32, 33, 127, 1000, 4097, 100003]
 def test_dot_norm(ctx, n, k):
     a, b = rnd(n, k, 1), rnd(n, k, 2)
     A, B = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, b)
-    assert relerr(A.MvDot(B), oracle.dot(a, b)) <= TOL * max(1.0, np.sqrt(n))
+    # a.b of two independent vectors cancels: the bound is relative to |a||b| (the condition of the sum), not to |a.b|
+    assert np.abs(A.MvDot(B) - oracle.dot(a, b)).max() <= TOL * np.sqrt(oracle.dot(a, a) * oracle.dot(b, b)).max()
     assert relerr(A.MvDot(A), oracle.dot(a, a)) <= TOL
     for t in (tb.NORM_ONE, tb.NORM_TWO, tb.NORM_INF):
         assert relerr(A.MvNorm(t), oracle.norm(a, t)) <= TOL
@@ -489,3 +490,102 @@ def test_lazy_copy_survives_every_write_to_its_source(ctx):
         cp.MvScale(0.5)
         assert np.array_equal(cp2.to_numpy(), a[:, [1]]), write
         assert np.array_equal(cp.to_numpy(), a[:, [1]] * 0.5), write
+
+
+# Fused update + Gram (update_gram.cu): MvTimesMatAddMv also leaves A^T V_new in the mailbox when the call pattern
+# predicts that MvTransMv(A, V) comes next (second pass of block Gram-Schmidt, BelosDGKSOrthoManager.hpp:1436-1455).
+# Same results as the two separate kernels (<= 1e-13 vs the oracle), never a stale block.
+UG_MIN_N = 148 * 28 * 4  # eligibility threshold of update_gram_fits on a 148-SM part
+
+
+@pytest.mark.parametrize("n", [UG_MIN_N, 20011, 100003, 262147])
+@pytest.mark.parametrize("p,q", [(8, 1), (13, 3), (16, 4), (57, 5), (100, 4), (200, 4), (208, 4), (209, 2), (40, 8), (256, 8)])
+@pytest.mark.parametrize("alpha,beta", [(-1.0, 1.0), (1.0, 0.0), (0.5, 2.0)])
+def test_fused_update_gram(ctx, n, p, q, alpha, beta):
+    if (n > 100003 and (p, q) not in [(200, 4), (256, 8), (13, 3)]) or (n == 20011 and alpha != -1.0):
+        pytest.skip("covered at the other sizes")
+    a, v, bm = rnd(n, p, 21), rnd(n, q, 22), rnd(p, q, 23) * 0.1
+    A, V = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, v)
+    if beta == 0.0:  # must not read V
+        V = tb.MultiVec.from_numpy(ctx, np.full((n, q), np.nan, order="F"))
+    # (a one-column CloneCopy is lazy and would be filled by the plain one-column update kernel instead)
+    Vold = V.CloneCopy() if q > 1 else None
+    ctx.set_fusion(True)  # (resets the call-pattern predictor: the next eligible update speculates)
+    l0, g0 = ctx.spec_gram_stats()
+    h0 = ctx.dot_hits()
+    V.MvTimesMatAddMv(alpha, A, bm, beta)
+    G = V.MvTransMv(2.0, A)
+    l1, g1 = ctx.spec_gram_stats()
+    assert (l1 - l0, g1 - g0) == (1, 1), "the update must have run fused and answered the MvTransMv"
+    vnew = oracle.times_mat_add_mv(alpha, a, bm, beta, v)
+    assert relerr(V.to_numpy(), vnew) <= TOL
+    assert relerr(G, oracle.trans_mv(2.0, a, vnew)) <= TOL
+    d_self = V.MvDot(V)
+    assert ctx.dot_hits() - h0 == q
+    assert relerr(d_self, oracle.dot(vnew, vnew)) <= TOL
+    if beta != 0.0 and Vold is not None:
+        d_old = V.MvDot(Vold)
+        assert ctx.dot_hits() - h0 == 2 * q
+        assert np.abs(d_old - oracle.dot(vnew, v)).max() <= TOL * np.sqrt(oracle.dot(vnew, vnew) * oracle.dot(v, v)).max()
+    # the separate kernels give the same block
+    ctx.set_fusion(False)
+    try:
+        assert relerr(V.MvTransMv(2.0, A), G) <= TOL
+    finally:
+        ctx.set_fusion(True)
+
+
+def test_fused_update_gram_memo_is_never_stale(ctx):
+    n, p, q = 50021, 24, 4
+    a, v, bm = rnd(n, p, 31), rnd(n, q, 32), rnd(p, q, 33) * 0.1
+    A, V = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, v)
+    ctx.set_fusion(True)
+    _, g0 = ctx.spec_gram_stats()
+    V.MvTimesMatAddMv(-1.0, A, bm, 1.0)
+    vnew = oracle.times_mat_add_mv(-1.0, a, bm, 1.0, v)
+    V.MvScale(0.5)  # V changed after the update: the remembered block is for other contents
+    assert relerr(V.MvTransMv(1.0, A), oracle.trans_mv(1.0, a, 0.5 * vnew)) <= TOL
+    assert ctx.spec_gram_stats()[1] == g0
+    # a different view of A (fewer columns) is a different product
+    ctx.set_fusion(True)
+    V.MvTimesMatAddMv(-1.0, A, bm, 1.0)
+    vnew2 = oracle.times_mat_add_mv(-1.0, a, bm, 1.0, 0.5 * vnew)
+    Asub = A.CloneView(list(range(p - 1)))
+    assert relerr(V.MvTransMv(1.0, Asub), oracle.trans_mv(1.0, a[:, : p - 1], vnew2)) <= TOL
+    assert ctx.spec_gram_stats()[1] == g0
+    # a column of A rewritten in between
+    ctx.set_fusion(True)
+    V.MvTimesMatAddMv(-1.0, A, bm, 1.0)
+    vnew3 = oracle.times_mat_add_mv(-1.0, a, bm, 1.0, vnew2)
+    A.CloneViewNonConst([3]).MvScale(2.0)
+    a2 = a.copy()
+    a2[:, 3] *= 2.0
+    assert relerr(V.MvTransMv(1.0, A), oracle.trans_mv(1.0, a2, vnew3)) <= TOL
+    assert ctx.spec_gram_stats()[1] == g0
+
+
+def test_fused_update_gram_follows_the_two_pass_pattern(ctx):
+    """Gram, update, Gram, update per block step (DGKS blkOrtho): after the first steps only the FIRST update of a
+    step runs fused (its Gram follows); the second one, whose product nobody asks for, goes to the plain kernel."""
+    n, p, q = 60013, 32, 4
+    a = rnd(n, p, 41)
+    vs = [rnd(n, q, 42), rnd(n, q, 43)]
+    A = tb.MultiVec.from_numpy(ctx, a)
+    Vs = [tb.MultiVec.from_numpy(ctx, v) for v in vs]
+    ctx.set_fusion(True)
+    l0, g0 = ctx.spec_gram_stats()
+    steps = 12
+    for s in range(steps):  # (consecutive block steps work on different blocks)
+        V = Vs[s % 2]
+        c1 = V.MvTransMv(1.0, A)
+        V.MvTimesMatAddMv(-1e-3, A, c1, 1.0)
+        c2 = V.MvTransMv(1.0, A)
+        V.MvTimesMatAddMv(-1e-3, A, c2, 1.0)
+        v = vs[s % 2]
+        v = v - 1e-3 * a @ (a.T @ v)
+        vs[s % 2] = v - 1e-3 * a @ (a.T @ v)
+    l1, g1 = ctx.spec_gram_stats()
+    for V, v in zip(Vs, vs):
+        assert relerr(V.to_numpy(), v) <= 1e-12
+    assert g1 - g0 >= steps - 2, "the second Gram of (almost) every step must come from the fused update"
+    assert l1 - l0 <= steps + 3, "the second update of a step must stop speculating after the first steps"

@@ -80,6 +80,12 @@ class Context:
         check(lib.b200_ctx_fusion_stats(self._h, C.byref(a)))
         return a.value
 
+    def spec_gram_stats(self):
+        """(updates that ran fused with the next Gram, MvTransMv calls answered from the mailbox)"""
+        a, b = c_i64(), c_i64()
+        check(lib.b200_ctx_spec_gram_stats(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def deferral_stats(self):
         """(lazy single-column copies never launched, single-column scales folded into the next skinny Gram)"""
         a, b = c_i64(), c_i64()
@@ -131,7 +137,8 @@ class MultiVec:
 
     def __del__(self):
         try:
-            if self._h:
+            # (after the context was closed its objects are gone with it: nothing to release, and nothing safe to touch)
+            if self._h and getattr(self.ctx, "_h", None):
                 lib.b200_mv_destroy(self._h)
                 self._h = None
         except Exception:
@@ -266,6 +273,7 @@ class Chebyshev:
 
     def __init__(self, op, degree=1, lambda_max=-1.0, eig_ratio=30.0, min_diag=0.0, eig_iters=10, seed=1):
         self.op = op  # must outlive the smoother
+        self.ctx = op.ctx
         self.params = ChebyParams(degree, lambda_max, eig_ratio, min_diag, eig_iters, seed)
         h = vp()
         check(lib.b200_cheby_create(op._h, C.byref(self.params), C.byref(h)))
@@ -273,7 +281,8 @@ class Chebyshev:
 
     def __del__(self):
         try:
-            if self._h:
+            # (after the context was closed its objects are gone with it: nothing to release, and nothing safe to touch)
+            if self._h and getattr(self.ctx, "_h", None):
                 lib.b200_cheby_destroy(self._h)
                 self._h = None
         except Exception:
@@ -307,7 +316,8 @@ class CrsOperator:
 
     def __del__(self):
         try:
-            if self._h:
+            # (after the context was closed its objects are gone with it: nothing to release, and nothing safe to touch)
+            if self._h and getattr(self.ctx, "_h", None):
                 lib.b200_op_destroy(self._h)
                 self._h = None
         except Exception:

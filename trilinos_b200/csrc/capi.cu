@@ -68,13 +68,27 @@ bool columns_overlap(const MV* a, const MV* b) {
 // (publish_result), folding all ranks' partials into the mailbox -- no host round trip, no exchange kernel.
 // The exchange numbers are taken here, i.e. in call order, which is the same on every rank.  Remembered
 // products that were still waiting in the recycled slot are dropped.
-bool fused_slot(Ctx* ctx, FusedDots* fd, size_t* src, int count) {
+bool fused_slot(Ctx* ctx, FusedDots* fd, size_t* src, int count, bool big = false) {
   if (!ctx->fuse || (ctx->nranks != 1 && !ctx->p2p)) return false;
-  const int slot = ctx->aux_next;
-  ctx->aux_next = (slot + 1) % kAuxSlots;
-  const size_t base = kAuxBase + (size_t)slot * kAuxSlotDoubles;
+  // big: one of the kSpecSlots larger slots below the small ones (fused update + Gram: dots, then A^T V_new)
+  int slot;
+  size_t base, cap, dev_off;
+  if (big) {
+    slot = ctx->spec_next;
+    ctx->spec_next = (slot + 1) % kSpecSlots;
+    base = kSpecBase + (size_t)slot * kSpecSlotDoubles;
+    cap = kSpecSlotDoubles;
+    dev_off = (size_t)kAuxSlots * kAuxSlotDoubles + (size_t)slot * kSpecSlotDoubles;
+    if (ctx->gmemo.valid && ctx->gmemo.src >= base && ctx->gmemo.src < base + cap) ctx->gmemo.valid = false;
+  } else {
+    slot = ctx->aux_next;
+    ctx->aux_next = (slot + 1) % kAuxSlots;
+    base = kAuxBase + (size_t)slot * kAuxSlotDoubles;
+    cap = kAuxSlotDoubles;
+    dev_off = (size_t)slot * kAuxSlotDoubles;
+  }
   for (int i = 0; i < kDotCache; ++i)
-    if (ctx->dots[i].seq != 0 && ctx->dots[i].src >= base && ctx->dots[i].src < base + kAuxSlotDoubles)
+    if (ctx->dots[i].seq != 0 && ctx->dots[i].src >= base && ctx->dots[i].src < base + cap)
       ctx->dots[i] = Ctx::DotEntry();
   fd->seq = ++ctx->seq;
   fd->ws = ctx->ws;
@@ -85,7 +99,7 @@ bool fused_slot(Ctx* ctx, FusedDots* fd, size_t* src, int count) {
   if (ctx->nranks == 1) {
     fd->out = ctx->mbox_d + base;
   } else {
-    fd->out = ctx->aux_d + (size_t)slot * kAuxSlotDoubles;
+    fd->out = ctx->aux_d + dev_off;
     fd->pub.nranks = ctx->nranks;
     fd->pub.rank = ctx->rank;
     fd->pub.count = count;
@@ -560,10 +574,32 @@ extern "C" int b200_mv_trans_mv(const b200_mv* mv, double alpha, const b200_mv* 
       for (int i = 0; i < p; ++i) B[(size_t)j * ldb + i] = 0.0;
     return 0;
   }
-  // (the top of the mailbox, from kAuxBase, holds fused-epilogue results that pending memo entries point to)
-  if ((size_t)p * q > kAuxBase)
+  // (the top of the mailbox, from kSpecBase, holds fused-epilogue results that pending memo entries point to)
+  if ((size_t)p * q > kSpecBase)
     return fail(B200_ERR_ARG, "MvTransMv: result block larger than the host mailbox");
   Ctx* ctx = mv->ctx;
+  // Is this the product the last (eligible) MvTimesMatAddMv could serve -- A^T V_new of the same columns?
+  // The predictor learns from the answer whether or not that update speculated; if it did, the block waits
+  // in the mailbox (update_gram.cu) and no kernel runs.
+  if (ctx->fuse && ctx->spec.open && (int)ctx->spec.a_ids.size() == p && (int)ctx->spec.v_ids.size() == q &&
+      !A->st->external && !mv->st->external) {
+    bool same = true;
+    for (int i = 0; i < p && same; ++i) same = ctx->spec.a_ids[(size_t)i] == A->st->ver[(size_t)A->cols[(size_t)i]];
+    for (int j = 0; j < q && same; ++j) same = ctx->spec.v_ids[(size_t)j] == mv->st->ver[(size_t)mv->cols[(size_t)j]];
+    if (same) {
+      ctx->spec.open = false;
+      ctx->spec.next_hit[ctx->spec.hist & 3u] = true;
+      ctx->spec.hist = (ctx->spec.hist << 1) | 1u;
+      Ctx::GramMemo& gm = ctx->gmemo;
+      if (gm.valid && gm.a_ids == ctx->spec.a_ids && gm.v_ids == ctx->spec.v_ids) {
+        B200_TRY(ctx->wait_flag(gm.seq));
+        for (int j = 0; j < q; ++j)
+          for (int i = 0; i < p; ++i) B[(size_t)j * ldb + i] = alpha * ctx->mbox_h[gm.src + (size_t)j * p + i];
+        ++ctx->gram_hits;
+        return 0;
+      }
+    }
+  }
   // one vector against <= 8 columns (findBasis): the skinny kernel applies pending column scales itself and
   // writes the scaled columns back -- the normalisation of the previous column costs no launch
   double scales[9];
@@ -668,11 +704,30 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
   // also emits x_new.x_new and x_new.x_old per column — the MvDot calls DGKS makes next.
   FusedDots fd;
   size_t src = 0;
-  const bool fuse = run_length(0, p, A, 0) == p && run_length(0, q, mv, 0) == q &&
-                    2 * q <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src, 2 * q);
+  const bool plain = run_length(0, p, A, 0) == p && run_length(0, q, mv, 0) == q;
+  // Fused update + Gram (update_gram.cu): when the call pattern says that MvTransMv(A, mv) comes next (the
+  // second pass of block Gram-Schmidt, BelosDGKSOrthoManager.hpp:1436-1455), the kernel also leaves A^T mv_new
+  // in the mailbox.  An eligible update that found no taker counts as a miss for the predictor.
+  const bool eligible = plain && !save_old && !A->st->external && !mv->st->external &&
+                        update_gram_fits(ctx, p, q, mv->n_global / std::max(1, ctx->nranks));  // (same answer on every rank)
+  bool spec = false;
+  if (eligible) {
+    Ctx::SpecState& sp = ctx->spec;
+    if (sp.open) {
+      sp.next_hit[sp.hist & 3u] = false;
+      sp.hist = sp.hist << 1;
+    }
+    spec = (sp.next_hit[sp.hist & 3u] || update_gram_always()) &&
+           (size_t)p * q + 2 * (size_t)q <= (size_t)kSpecSlotDoubles &&
+           fused_slot(ctx, &fd, &src, p * q + 2 * q, true);
+  }
+  const bool fuse = spec || (plain && 2 * q <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src, 2 * q));
   std::vector<uint64_t> old_id(q);
   for (int j = 0; j < q; ++j) old_id[j] = mv->id(j);
-  for (int jv = 0; jv < q;) {
+  if (spec && mv->n_local > 0)
+    B200_TRY(launch_update_gram(ctx, mv->col(0), mv->ld, q, A->col(0), A->ld, p, mv->n_local, ctx->dB, p,
+                                alpha, beta, fd));
+  for (int jv = 0; jv < q && !spec;) {
     const int lv = run_length(jv, q, mv, jv);
     bool first = true;
     for (int ja = 0; ja < p;) {
@@ -691,13 +746,30 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
     ++ctx->lazy_saved;
   }
   if (fuse && mv->n_local == 0)  // no kernel ran: the fused sums are zero, but must still be handed over
-    B200_TRY(launch_zero_result(ctx, fd.out, 2 * q, fd.pub));
+    B200_TRY(launch_zero_result(ctx, fd.out, spec ? p * q + 2 * q : 2 * q, fd.pub));
   if (fuse)
     for (int j = 0; j < q; ++j) {
       const uint64_t nid = mv->id(j);
       ctx->remember_dot(nid, nid, 0.0, fd.seq, src + 2 * j);
       if (beta != 0.0) ctx->remember_dot(nid, old_id[j], 0.0, fd.seq, src + 2 * j + 1);
     }
+  if (eligible) {
+    Ctx::SpecState& sp = ctx->spec;
+    sp.a_ids.resize((size_t)p);
+    sp.v_ids.resize((size_t)q);
+    for (int i = 0; i < p; ++i) sp.a_ids[(size_t)i] = A->id(i);
+    for (int j = 0; j < q; ++j) sp.v_ids[(size_t)j] = mv->id(j);
+    sp.open = true;
+    if (spec) {
+      Ctx::GramMemo& gm = ctx->gmemo;
+      gm.a_ids = sp.a_ids;
+      gm.v_ids = sp.v_ids;
+      gm.seq = fd.seq;
+      gm.src = src + 2 * (size_t)q;
+      gm.valid = true;
+      ++ctx->gram_spec;
+    }
+  }
   return 0;
 }
 

@@ -366,7 +366,7 @@ extern "C" int b200_ctx_create(int device, b200_ctx** out) {
   B200_CUDA(cudaMalloc((void**)&c->ticket, kTicketBytes));
   B200_CUDA(cudaMemset(c->ticket, 0, kTicketBytes));
   B200_CUDA(cudaMalloc((void**)&c->red_d, kMailboxDoubles * sizeof(double)));
-  B200_CUDA(cudaMalloc((void**)&c->aux_d, (size_t)kAuxSlots * kAuxSlotDoubles * sizeof(double)));
+  B200_CUDA(cudaMalloc((void**)&c->aux_d, ((size_t)kAuxSlots * kAuxSlotDoubles + (size_t)kSpecSlots * kSpecSlotDoubles) * sizeof(double)));
   B200_CUDA(cudaMalloc((void**)&c->dB, kStageSlotBytes));
   B200_CUDA(cudaMalloc((void**)&c->dBpack, kPackBytes));
   B200_CUDA(cudaHostAlloc((void**)&c->stage_h, kStageSlots * kStageSlotBytes, cudaHostAllocDefault));
@@ -522,12 +522,21 @@ extern "C" int b200_ctx_set_fusion(b200_ctx* c, int on) {
   if (!c) return fail(B200_ERR_ARG, "null context");
   c->fuse = on != 0;
   for (auto& e : c->dots) e = Ctx::DotEntry();
+  c->gmemo.valid = false;
+  c->spec = Ctx::SpecState();
   return 0;
 }
 
 extern "C" int b200_ctx_fusion_stats(const b200_ctx* c, int64_t* dot_hits) {
   if (!c) return fail(B200_ERR_ARG, "null context");
   if (dot_hits) *dot_hits = c->dot_hits;
+  return 0;
+}
+
+extern "C" int b200_ctx_spec_gram_stats(const b200_ctx* c, int64_t* launches, int64_t* hits) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  if (launches) *launches = c->gram_spec;
+  if (hits) *hits = c->gram_hits;
   return 0;
 }
 

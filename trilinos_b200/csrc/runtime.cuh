@@ -29,6 +29,11 @@ constexpr int kDotCache = 64;                   // remembered column dot product
 constexpr int kAuxSlots = 32;                   // mailbox slots for results of fused epilogues
 constexpr int kAuxSlotDoubles = 64;             // <= 32 columns x {self, with-old}
 constexpr size_t kAuxBase = kMailboxDoubles - (size_t)kAuxSlots * kAuxSlotDoubles;
+// Two larger slots below them for the fused update + Gram kernel (update_gram.cu): 2q dot products followed
+// by the p x q block A^T V_new (p <= 256, q <= 8) that the next MvTransMv is expected to ask for.
+constexpr int kSpecSlots = 2;
+constexpr int kSpecSlotDoubles = 2112;
+constexpr size_t kSpecBase = kAuxBase - (size_t)kSpecSlots * kSpecSlotDoubles;
 constexpr size_t kStageSlotBytes = 512u << 10; // host B blocks for MvTimesMatAddMv
 constexpr size_t kPackBytes = 1u << 20;        // the same block in DMMA fragment order (16 -> 24 columns)
 
@@ -148,6 +153,24 @@ struct Ctx {
   int64_t dot_hits = 0;
   int64_t pending = 0;        // deferred scales + lazy copies outstanding (0: the prep_* hooks return at once)
   int64_t lazy_saved = 0, scale_folded = 0;  // launches that never happened (diagnostics)
+  // Gram memo: A^T V of the listed columns was produced by the fused update + Gram kernel and waits at
+  // mbox_h[src + k p + col] (once flag >= seq); consulted by MvTransMv.
+  struct GramMemo {
+    std::vector<uint64_t> a_ids, v_ids;
+    uint64_t seq = 0;
+    size_t src = 0;
+    bool valid = false;
+  } gmemo;
+  // Call-pattern predictor for that kernel: did the MvTransMv(A, V) that the last eligible update could have
+  // served actually come?  spec_next[h] = outcome that followed outcome history h (two calls deep) last time.
+  struct SpecState {
+    std::vector<uint64_t> a_ids, v_ids;  // the last eligible update (whether it speculated or not)
+    bool open = false;                   // ... and no MvTransMv has matched it yet
+    unsigned hist = 0;
+    bool next_hit[4] = {true, true, true, true};
+  } spec;
+  int spec_next = 0;                     // next big slot
+  int64_t gram_hits = 0, gram_spec = 0;  // memo answers / speculative launches (diagnostics)
   void remember_dot(uint64_t a, uint64_t b, double val, uint64_t seq = 0, size_t src = 0);
   // true (and *val set, waiting for the producing kernel if needed) if the product is known
   bool recall_dot(uint64_t a, uint64_t b, double* val, int* rc);
@@ -388,6 +411,12 @@ bool gram_is_skinny(int p, int q);
 int launch_update(Ctx*, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
                   int64_t n, const double* dB, int ldb, double alpha, double beta,
                   const FusedDots* fused = nullptr, double* save_old = nullptr);
+// update_gram.cu : the same update; fused.out[0..2q) = the dot products, fused.out[2q + k p + col] = A^T V_new
+bool update_gram_fits(Ctx*, int p, int q, int64_t n);
+bool update_gram_always();
+int launch_update_gram(Ctx*, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
+                       int64_t n, const double* dB, int ldb, double alpha, double beta,
+                       const FusedDots& fused);
 // spmm.cu
 // fused != nullptr (single rank, stream kernel only): also emit sum y(:,k)^2 into fused->out[k]
 int launch_spmm(Ctx*, const Op* op, const int32_t* rows, int64_t nrows, const double* x,

@@ -1,0 +1,465 @@
+// MvTimesMatAddMv fused with the Gram product the orthogonalisation asks for next.
+//
+// Block Gram-Schmidt in Belos always makes two passes over the basis per block step
+// (BelosDGKSOrthoManager.hpp:1400-1472, max_blk_ortho_ = 2; BelosICGSOrthoManager.hpp the same loop):
+//     C  = Q^T X          (MvTransMv)           X <- X - Q C    (MvTimesMatAddMv)
+//     C2 = Q^T X          (MvTransMv)           X <- X - Q C2   (MvTimesMatAddMv)
+// i.e. the basis Q (n x p, the only large operand) crosses HBM four times.  The second Gram reads
+// exactly the tile of Q the first update has just had in shared memory.  This kernel does the update
+// and, from the same staged tile, accumulates Q^T X_new: the result waits in the host mailbox, and the
+// MvTransMv call that follows is answered without a launch (capi.cu, gram memo, keyed by the content
+// ids of the columns, as the fused dot products already are).  One pass over Q of four disappears.
+//
+// Reference semantics are those of the two separate calls:
+//   MvTimesMatAddMv  belos/epetra/src/BelosEpetraAdapter.cpp:421-435 -> Epetra_MultiVector::Multiply('N','N')
+//   MvTransMv        belos/epetra/src/BelosEpetraAdapter.cpp:480-495 -> Epetra_MultiVector::Multiply('T','N') + SumAll
+//
+// Design (HBM-bound: algorithmic bytes are those of the update alone, 8 n (p + 2 q)):
+//   * persistent grid, one CTA per SM, contiguous range of R-row tiles per CTA.  A tile (R rows x all
+//     p <= 256 basis columns) must be resident when X_new of its rows is known, so the ring is two whole
+//     tiles; each tile arrives as ceil(p/16) TMA boxes (R rows x 16 columns) with an mbarrier each, so
+//     the update starts on the first box while the rest is in flight.
+//   * both products run on the FP64 tensor cores (mma.sync.m8n8k4.f64): a DMMA accumulator block costs
+//     2 registers per lane, so ONE warp can hold Q^T X_new for all 256 columns (64 registers) -- with
+//     SIMT lanes-over-rows accumulators that would be 32x replicated and the kernel could not be
+//     row-tile-major.  q <= 8 right-hand sides; unused accumulator columns are fed zeros.
+//   * warp roles: 4 update warps + 4 Gram warps (one of each per SM sub-partition: each owns a quarter
+//     of the FP64 pipe) + 1 producer.  Update warp w owns the 8-row groups {w, w+4, ...} of the tile for
+//     all columns (two interleaved accumulator chains per group), reads the old X from global memory
+//     before the column loop, writes X_new to global memory and into a small shared buffer (double
+//     buffered), and keeps the two DGKS dot products per column (x_new.x_new, x_new.x_old) as the plain
+//     update kernels do.  The Gram warps then sweep the same tile: (4-row step g, 8-column block cb) goes
+//     to warp (g + cb) mod 4, so the four warps stay balanced for any p.
+//   * R = 28 (mod 32): the column stride is 12 (mod 16) doubles, every fragment load of either phase is
+//     two conflict-free wavefronts, and the 8-row groups deal evenly to the 4 update warps.
+//   * per-CTA partials (p q Gram entries + 2 q dots) -> workspace; the deterministic two-level fold and
+//     the hand-over to the host (or the peer exchange, multi-rank) are those of the other kernels.
+#include <cuda.h>
+
+#include "device_utils.cuh"
+#include "runtime.cuh"
+
+#include <algorithm>
+#include <cstdlib>
+
+namespace b200 {
+
+int make_tmap(CUtensorMap* tm, const double* base, int64_t n, int ncols, int64_t ld, int box_rows,
+              int box_cols);
+
+namespace {
+
+constexpr int kCW = 16;          // basis columns per TMA box
+constexpr int kMaxChunks = 16;   // p <= 256
+constexpr int kNU = 4, kNG = 4;  // update / Gram warps
+constexpr int kMaxCB = 32;       // 8-column blocks (p <= 256)
+constexpr int kMaxNB = 4;        // tile buffers
+constexpr int kThreadsUG = (kNU + kNG + 1) * 32;
+constexpr size_t kSmemUG = 224u << 10;
+
+struct UGArgs {
+  double* V;
+  const double* B;  // p x q, leading dimension ldb (device)
+  int64_t ldv, n, ntiles;
+  int p, q, ldb, rows, nchunk, nbuf, dbg;
+  double alpha, beta;
+  FusedDots fd;     // out[0 .. 2q): dot products, out[2q + k p + col]: (A^T V_new)(col, k)
+};
+
+// shared-memory geometry, the same on host and device
+struct UGSmem {
+  uint32_t bs_bytes, x_bytes, chunk_bytes, tile_bytes;
+  B200_HD UGSmem(int R, int nchunk, int q) {
+    bs_bytes = (uint32_t)nchunk * kCW * 64u;                  // B as [column][8], zero padded
+    x_bytes = ((uint32_t)(q * R) * 8u + 127u) & ~127u;        // one X_new buffer
+    chunk_bytes = (uint32_t)(R * kCW) * 8u;
+    tile_bytes = chunk_bytes * (uint32_t)nchunk;
+  }
+  B200_HD size_t total(int nbuf) const { return (size_t)bs_bytes + (size_t)nbuf * (x_bytes + tile_bytes) + 128 + 64; }
+};
+
+struct UGBars {
+  uint64_t full[kMaxNB][kMaxChunks], empty[kMaxNB], xfull[kMaxNB];
+};
+
+#define B200_DMMA(c0, c1, a, b)                                                                \
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" \
+               : "+d"(c0), "+d"(c1)                                                            \
+               : "d"(a), "d"(b))
+
+// ------------------------------------------------------------------ update warps
+// K = 8-row groups per warp (R = 32 K - 4): every loop over the groups is unrolled without predicates.  (A first
+// version unrolled to the maximum and predicated each slot on a run-time count: the chain ISETP -> @P LDS -> @P DMMA
+// through ONE predicate register serialised all 8 slots, ~280 cycles per 4-column step whatever the count --
+// 5x slower than the two separate kernels, profiles/r2_ug_predication_s8.txt.)
+template <int K>
+__device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UGBars& bar, unsigned char* xbuf0,
+                                            unsigned char* tile0, const double* Bs, int64_t t_begin, int ntile_cta,
+                                            int warp, int lane, double (&dself)[2], double (&dold)[2]) {
+  const int R = u.rows, q = u.q, nchunk = u.nchunk;
+  const uint32_t colstride = (uint32_t)R * 8u;
+  // A fragment: lane l = (row l/4 of the group, basis column l%4 of the step); B: (k = l%4, n = l/4)
+  const uint32_t a_lane = (uint32_t)(lane & 3) * colstride + (uint32_t)(lane >> 2) * 8u + (uint32_t)warp * 64u;
+  const uint32_t b_addr = smem_u32(Bs) + (uint32_t)((lane & 3) * 8 + (lane >> 2)) * 8u;
+  const int c0 = 2 * (lane & 3);  // this lane's output columns c0, c0 + 1
+  int tb = 0;
+  uint32_t par = 0;
+  for (int t = 0; t < ntile_cta; ++t) {
+    const int64_t r0 = (t_begin + t) * R;
+    double acc[K][2][2];
+#pragma unroll
+    for (int i = 0; i < K; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) acc[i][0][j] = acc[i][1][j] = 0.0;
+    const uint32_t tile_addr = smem_u32(tile0) + (uint32_t)tb * g.tile_bytes + a_lane;
+    for (int c = 0; c < nchunk; ++c) {
+      mbar_wait(&bar.full[tb][c], par);
+      if (u.dbg & 2) continue;
+      const uint32_t ch_addr = tile_addr + (uint32_t)c * g.chunk_bytes;
+      const uint32_t bc_addr = b_addr + (uint32_t)(c * kCW) * 64u;
+      // columns >= p of the last box are zero-filled by the TMA unit and meet zero rows of Bs: no column predicate
+      double b[kCW / 4];
+#pragma unroll
+      for (int ks = 0; ks < kCW / 4; ++ks) b[ks] = lds_f64(bc_addr + (uint32_t)(4 * ks) * 64u);
+#pragma unroll
+      for (int ks = 0; ks < kCW / 4; ++ks) {
+        double a[K];
+#pragma unroll
+        for (int i = 0; i < K; ++i) a[i] = lds_f64(ch_addr + (uint32_t)(4 * ks) * colstride + (uint32_t)(kNU * i) * 64u);
+#pragma unroll
+        for (int i = 0; i < K; ++i) B200_DMMA(acc[i][ks & 1][0], acc[i][ks & 1][1], a[i], b[ks]);
+      }
+    }
+    // C fragment: lane l holds rows l/4, columns 2 (l%4) + {0,1}.  The old X tile came with the first box
+    // (rows >= n zero-filled); X_new replaces it in place, element by element, for the Gram warps.
+    double* xb = reinterpret_cast<double*>(xbuf0 + (size_t)tb * g.x_bytes);
+#pragma unroll
+    for (int i = 0; i < K; ++i) {
+      const int rt = 8 * (warp + kNU * i) + (lane >> 2);
+      const int64_t row = r0 + rt;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        if (c0 + j < q && rt < R) {
+          const double s = acc[i][0][j] + acc[i][1][j];
+          double o;
+          if (u.beta == 0.0) {
+            o = row < u.n ? u.alpha * s : 0.0;
+            dself[j] = fma(o, o, dself[j]);
+          } else {
+            const double v = xb[(c0 + j) * R + rt];
+            o = fma(u.alpha, s, u.beta * v);
+            dself[j] = fma(o, o, dself[j]);
+            dold[j] = fma(o, v, dold[j]);
+          }
+          if (row < u.n) u.V[(size_t)(c0 + j) * u.ldv + row] = o;
+          xb[(c0 + j) * R + rt] = o;
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) {
+      mbar_arrive(&bar.xfull[tb]);
+      mbar_arrive(&bar.empty[tb]);
+    }
+    if (++tb == u.nbuf) { tb = 0; par ^= 1u; }
+  }
+}
+
+// ------------------------------------------------------------------ Gram warps
+// NCB = 8-column blocks of A (compile time: no predicated slots, see update_role).  Warp wg takes the 4-row steps
+// g = wg (mod 4) of every tile for all blocks; R / 4 = 8 K - 1 steps deal to 4 warps within one step of each other.
+// Few blocks: two accumulator sets alternate by step, so that consecutive DMMAs of a block do not wait for each other.
+template <int NCB>
+__device__ __forceinline__ void gram_role(const UGArgs& u, const UGSmem& g, UGBars& bar, unsigned char* xbuf0,
+                                          unsigned char* tile0, int ntile_cta, int wg, int lane,
+                                          double (&gacc)[kMaxCB][2]) {
+  constexpr int NS = NCB <= 4 ? 2 : 1;
+  const int R = u.rows, nchunk = u.nchunk;
+  const int ng = R >> 2;
+  const uint32_t colstride = (uint32_t)R * 8u;
+  // A^T fragment: lane l = (basis column l/4 of the block, row l%4 of the step); V_new: (k = l%4, n = l/4)
+  const uint32_t frag = (uint32_t)(lane >> 2) * colstride + (uint32_t)(lane & 3) * 8u;
+  const bool has_rhs = (lane >> 2) < u.q;
+  const uint32_t blk_stride = 8u * colstride;
+  double acc[NS][NCB][2];
+#pragma unroll
+  for (int s = 0; s < NS; ++s)
+#pragma unroll
+    for (int cb = 0; cb < NCB; ++cb) acc[s][cb][0] = acc[s][cb][1] = 0.0;
+  int tb = 0;
+  uint32_t par = 0;
+  for (int t = 0; t < ntile_cta; ++t) {
+    mbar_wait(&bar.xfull[tb], par);
+    for (int c = 0; c < nchunk; ++c) mbar_wait(&bar.full[tb][c], par);  // (already complete: acquire of the TMA writes)
+    const uint32_t a_addr = smem_u32(tile0) + (uint32_t)tb * g.tile_bytes + frag;
+    const uint32_t x_addr = smem_u32(xbuf0) + (uint32_t)tb * g.x_bytes + frag;
+    if (!(u.dbg & 1)) {
+      int g4 = wg;
+      for (; g4 + 4 * (NS - 1) < ng; g4 += 4 * NS) {
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+          const uint32_t row = (uint32_t)(g4 + 4 * s) * 32u;  // 4 rows x 8 bytes
+          const double b = has_rhs ? lds_f64(x_addr + row) : 0.0;
+          double a[NCB];
+#pragma unroll
+          for (int cb = 0; cb < NCB; ++cb) a[cb] = lds_f64(a_addr + row + (uint32_t)cb * blk_stride);
+#pragma unroll
+          for (int cb = 0; cb < NCB; ++cb) B200_DMMA(acc[s][cb][0], acc[s][cb][1], a[cb], b);
+        }
+      }
+      if (NS == 2 && g4 < ng) {  // odd step left over
+        const uint32_t row = (uint32_t)g4 * 32u;
+        const double b = has_rhs ? lds_f64(x_addr + row) : 0.0;
+        double a[NCB];
+#pragma unroll
+        for (int cb = 0; cb < NCB; ++cb) a[cb] = lds_f64(a_addr + row + (uint32_t)cb * blk_stride);
+#pragma unroll
+        for (int cb = 0; cb < NCB; ++cb) B200_DMMA(acc[0][cb][0], acc[0][cb][1], a[cb], b);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bar.empty[tb]);
+    if (++tb == u.nbuf) { tb = 0; par ^= 1u; }
+  }
+#pragma unroll
+  for (int cb = 0; cb < NCB; ++cb) {
+    gacc[cb][0] = NS == 2 ? acc[0][cb][0] + acc[NS - 1][cb][0] : acc[0][cb][0];
+    gacc[cb][1] = NS == 2 ? acc[0][cb][1] + acc[NS - 1][cb][1] : acc[0][cb][1];
+  }
+}
+
+// run-time block count -> compile-time instantiation
+template <int LO, int HI>
+__device__ __forceinline__ void gram_dispatch(int ncb, const UGArgs& u, const UGSmem& g, UGBars& bar,
+                                              unsigned char* xbuf0, unsigned char* tile0, int ntile_cta, int wg,
+                                              int lane, double (&gacc)[kMaxCB][2]) {
+  if constexpr (LO == HI) {
+    gram_role<LO>(u, g, bar, xbuf0, tile0, ntile_cta, wg, lane, gacc);
+  } else {
+    constexpr int MID = (LO + HI) / 2;
+    if (ncb <= MID) gram_dispatch<LO, MID>(ncb, u, g, bar, xbuf0, tile0, ntile_cta, wg, lane, gacc);
+    else gram_dispatch<MID + 1, HI>(ncb, u, g, bar, xbuf0, tile0, ntile_cta, wg, lane, gacc);
+  }
+}
+
+__global__ void __launch_bounds__(kThreadsUG, 1)
+    update_gram_kernel(const __grid_constant__ UGArgs u, const __grid_constant__ CUtensorMap tmA,
+                       const __grid_constant__ CUtensorMap tmV) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ UGBars bar;
+  __shared__ double dred[kNU][16];
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int R = u.rows, p = u.p, q = u.q, nchunk = u.nchunk;
+  const UGSmem g(R, nchunk, q);
+  unsigned char* base = reinterpret_cast<unsigned char*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  double* Bs = reinterpret_cast<double*>(base);
+  unsigned char* xbuf0 = base + g.bs_bytes;
+  unsigned char* tile0 = xbuf0 + (size_t)u.nbuf * g.x_bytes;
+  const int64_t t_begin = u.ntiles * blockIdx.x / gridDim.x;
+  const int64_t t_end = u.ntiles * (blockIdx.x + 1) / gridDim.x;
+  const int ntile_cta = (int)(t_end - t_begin);
+
+  for (int e = threadIdx.x; e < nchunk * kCW * 8; e += kThreadsUG) {
+    const int j = e >> 3, c = e & 7;
+    Bs[e] = (j < p && c < q) ? u.B[(size_t)c * u.ldb + j] : 0.0;
+  }
+  if (threadIdx.x == 0) {
+    for (int b = 0; b < u.nbuf; ++b) {
+      for (int c = 0; c < nchunk; ++c) mbar_init(&bar.full[b][c], 1);
+      mbar_init(&bar.empty[b], kNU + kNG);
+      mbar_init(&bar.xfull[b], kNU);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  double gacc[kMaxCB][2];      // Gram warps: (A^T V_new) blocks, kept over all tiles of the CTA
+  double dself[2], dold[2];    // update warps: dot products of this lane's two columns
+#pragma unroll
+  for (int i = 0; i < kMaxCB; ++i) gacc[i][0] = gacc[i][1] = 0.0;
+  dself[0] = dself[1] = dold[0] = dold[1] = 0.0;
+
+  if (warp == kNU + kNG) {
+    // ------------------------------------------------------------------ producer (one thread)
+    if (lane == 0) {
+      const uint64_t pol = l2_policy_evict_first();
+      const uint64_t pol_v = l2_policy_evict_last();  // X is the next kernel's operand
+      int tb = 0;
+      uint32_t par = 0;
+      for (int t = 0; t < ntile_cta; ++t) {
+        mbar_wait(&bar.empty[tb], par ^ 1u);
+        const int r0 = (int)((t_begin + t) * R);
+        unsigned char* dst = tile0 + (size_t)tb * g.tile_bytes;
+        for (int c = 0; c < nchunk; ++c) {
+          // the old X tile (beta != 0) travels with the first box: [column][R], the layout X_new is left in
+          const bool with_x = c == 0 && u.beta != 0.0;
+          mbar_expect_tx(&bar.full[tb][c], g.chunk_bytes + (with_x ? (uint32_t)(q * R) * 8u : 0u));
+          tma_load_2d(dst + (size_t)c * g.chunk_bytes, &tmA, r0, c * kCW, &bar.full[tb][c], pol);
+          if (with_x) tma_load_2d(xbuf0 + (size_t)tb * g.x_bytes, &tmV, r0, 0, &bar.full[tb][c], pol_v);
+        }
+        if (++tb == u.nbuf) { tb = 0; par ^= 1u; }
+      }
+    }
+    __syncwarp();
+  } else if (warp < kNU) {
+    switch ((R + 4) >> 5) {
+      case 1: update_role<1>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
+      case 2: update_role<2>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
+      case 3: update_role<3>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
+      case 4: update_role<4>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
+      case 5: update_role<5>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
+      case 6: update_role<6>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
+      case 7: update_role<7>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
+      default: update_role<8>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
+    }
+  } else {
+    gram_dispatch<1, kMaxCB>((p + 7) >> 3, u, g, bar, xbuf0, tile0, ntile_cta, warp - kNU, lane, gacc);
+  }
+
+  // ---- CTA partials: Gram blocks of the 4 Gram warps through shared memory (the tile buffers are free:
+  // every load was consumed), dot products of the 4 update warps
+  __syncthreads();
+  const int ncb8 = (p + 7) >> 3;
+  double* red = reinterpret_cast<double*>(tile0);  // [Gram warp][8 ncb8 columns][8]
+  if (warp >= kNU && warp < kNU + kNG) {
+    const int wg = warp - kNU;
+#pragma unroll
+    for (int cb = 0; cb < kMaxCB; ++cb) {
+      if (cb < ncb8) {
+        double* r = red + ((size_t)(wg * ncb8 + cb) * 8 + (lane >> 2)) * 8 + 2 * (lane & 3);
+        r[0] = gacc[cb][0];
+        r[1] = gacc[cb][1];
+      }
+    }
+  } else if (warp < kNU) {
+    // lanes with equal l%4 hold the same columns: fold over l/4
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      double a = dself[j], b = dold[j];
+#pragma unroll
+      for (int o = 4; o < 32; o <<= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+      }
+      if (lane < 4) {
+        dred[warp][2 * (2 * lane + j)] = a;
+        dred[warp][2 * (2 * lane + j) + 1] = b;
+      }
+    }
+  }
+  __syncthreads();
+  const int ngram = p * q, nent = ngram + 2 * q;
+  double* wsc = u.fd.ws + (size_t)blockIdx.x * nent;
+  for (int e = threadIdx.x; e < nent; e += kThreadsUG) {
+    double s = 0.0;
+    if (e < ngram) {
+      const int k = e / p, col = e - k * p;
+#pragma unroll
+      for (int w = 0; w < kNG; ++w) s += red[((size_t)w * ncb8 * 8 + col) * 8 + k];
+    } else {
+#pragma unroll
+      for (int w = 0; w < kNU; ++w) s += dred[w][e - ngram];
+    }
+    wsc[e] = s;
+  }
+  const bool fin = fold_partials_tall<kThreadsUG>(u.fd.ws, u.fd.ticket, nent, (int)gridDim.x, (int)blockIdx.x,
+                                                  [&](int e, double s) {
+                                                    if (e < ngram) u.fd.out[2 * q + e] = s;
+                                                    else u.fd.out[e - ngram] = s;
+                                                  });
+  if (!fin) return;
+  publish_result(u.fd.pub);
+}
+
+// rows per tile: R = 28 (mod 32); at least two tile buffers (+ the staged B + the X_new buffers) must fit.  Among
+// the candidates that fit, the one that leaves the shortest idle tail when the tiles are dealt to the CTAs
+// (larger tiles amortise the per-tile hand-overs: a 4 % longer tail is accepted for them).
+int ug_bufs(int R, int p, int q) {
+  const UGSmem g(R, (p + kCW - 1) / kCW, q);
+  int nb = kMaxNB;
+  while (nb >= 2 && g.total(nb) > kSmemUG) --nb;
+  return nb >= 2 ? nb : 0;
+}
+
+int ug_pick_rows(int p, int q, int64_t n, int num_sms) {
+  int best = 0;
+  int64_t min_cost = 0;
+  int64_t cost[8];
+  int cand[8];
+  int nc = 0;
+  for (int R = 28; R <= 252; R += 32) {
+    if (ug_bufs(R, p, q) == 0) break;
+    const int64_t nt = (n + R - 1) / R;
+    const int64_t grid = std::min<int64_t>(num_sms, nt);
+    cand[nc] = R;
+    cost[nc] = (nt + grid - 1) / grid * R;
+    if (nc == 0 || cost[nc] < min_cost) min_cost = cost[nc];
+    ++nc;
+  }
+  for (int i = 0; i < nc; ++i)
+    if (cost[i] * 100 <= min_cost * 104) best = cand[i];
+  return best;
+}
+
+}  // namespace
+
+static int spec_mode() {  // B200_SPEC_GRAM: 0 never, 1 (default) when the call pattern predicts a hit, 2 always
+  static const int m = [] {
+    const char* e = getenv("B200_SPEC_GRAM");
+    return e ? atoi(e) : 1;
+  }();
+  return m;
+}
+
+// can launch_update_gram take this shape at all?
+bool update_gram_fits(Ctx* ctx, int p, int q, int64_t n) {
+  if (spec_mode() == 0 || !ctx->fuse) return false;
+  if (p < 8 || p > kMaxCB * 8 || q < 1 || q > 8) return false;
+  if (n < (int64_t)ctx->num_sms * 28 * 4) return false;  // a few tiles per CTA, or the pipeline never fills
+  return ug_pick_rows(p, q, n, ctx->num_sms) > 0;
+}
+bool update_gram_always() { return spec_mode() >= 2; }
+
+// V = alpha A B + beta V as launch_update does; in addition fd.out[0 .. 2q) = {x_new.x_new, x_new.x_old}
+// per column and fd.out[2q + k p + col] = sum_rows A(:, col) V_new(:, k)
+int launch_update_gram(Ctx* ctx, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
+                       int64_t n, const double* dB, int ldb, double alpha, double beta,
+                       const FusedDots& fd) {
+  UGArgs u;
+  u.V = V; u.B = dB; u.ldv = ldv; u.n = n; u.p = p; u.q = q; u.ldb = ldb;
+  u.alpha = alpha; u.beta = beta; u.fd = fd;
+  int R = ug_pick_rows(p, q, n, ctx->num_sms);
+  if (const char* e = getenv("B200_UG_ROWS")) R = atoi(e);
+  u.dbg = getenv("B200_UG_DBG") ? atoi(getenv("B200_UG_DBG")) : 0;
+  if (R <= 0) return fail(B200_ERR_ARG, "MvTimesMatAddMv: fused update + Gram does not fit (internal)");
+  u.rows = R;
+  u.nchunk = (p + kCW - 1) / kCW;
+  u.nbuf = ug_bufs(R, p, q);
+  if (const char* e = getenv("B200_UG_BUFS")) u.nbuf = std::max(2, std::min(u.nbuf, atoi(e)));
+  if (u.nbuf < 2 || R % 32 != 28 || R > 252)
+    return fail(B200_ERR_ARG, "MvTimesMatAddMv: fused update + Gram: bad tile height (internal)");
+  u.ntiles = (n + R - 1) / R;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->num_sms, u.ntiles));
+  const size_t nent = (size_t)p * q + 2 * (size_t)q;
+  if (nent * (grid + grid / 16 + 1) * sizeof(double) > kWorkspaceBytes)
+    return fail(B200_ERR_ARG, "MvTimesMatAddMv: partial-sum workspace too small");
+  CUtensorMap tmA, tmV;
+  B200_TRY(make_tmap(&tmA, A, n, p, lda, R, kCW));
+  B200_TRY(make_tmap(&tmV, V, n, q, ldv, R, q));
+  static unsigned attr_devs = 0;  // bit per device: the attribute is per device, not per process
+  if (!(attr_devs & (1u << (ctx->device & 31)))) {
+    B200_CUDA(cudaFuncSetAttribute(update_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)kSmemUG));
+    attr_devs |= 1u << (ctx->device & 31);
+  }
+  ctx->t_begin(K_UPDATE, 8.0 * n * ((double)p + (beta == 0.0 ? 1.0 : 2.0) * q));
+  update_gram_kernel<<<grid, kThreadsUG, UGSmem(R, u.nchunk, q).total(u.nbuf), ctx->stream>>>(u, tmA, tmV);
+  ++ctx->launches;
+  ctx->t_end();
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace b200
