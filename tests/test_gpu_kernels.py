@@ -499,10 +499,10 @@ UG_MIN_N = 148 * 28 * 4  # eligibility threshold of update_gram_fits on a 148-SM
 
 
 @pytest.mark.parametrize("n", [UG_MIN_N, 20011, 100003, 262147])
-@pytest.mark.parametrize("p,q", [(8, 1), (13, 3), (16, 4), (57, 5), (100, 4), (200, 4), (208, 4), (209, 2), (40, 8), (256, 8)])
+@pytest.mark.parametrize("p,q", [(24, 1), (29, 3), (32, 4), (57, 5), (100, 4), (200, 4), (208, 4), (209, 2), (40, 8), (256, 8)])
 @pytest.mark.parametrize("alpha,beta", [(-1.0, 1.0), (1.0, 0.0), (0.5, 2.0)])
 def test_fused_update_gram(ctx, n, p, q, alpha, beta):
-    if (n > 100003 and (p, q) not in [(200, 4), (256, 8), (13, 3)]) or (n == 20011 and alpha != -1.0):
+    if (n > 100003 and (p, q) not in [(200, 4), (256, 8), (29, 3)]) or (n == 20011 and alpha != -1.0):
         pytest.skip("covered at the other sizes")
     a, v, bm = rnd(n, p, 21), rnd(n, q, 22), rnd(p, q, 23) * 0.1
     A, V = tb.MultiVec.from_numpy(ctx, a), tb.MultiVec.from_numpy(ctx, v)

@@ -51,17 +51,17 @@ namespace {
 
 constexpr int kCW = 16;          // basis columns per TMA box
 constexpr int kMaxChunks = 16;   // p <= 256
-constexpr int kNU = 4, kNG = 4;  // update / Gram warps
+constexpr int kNU = 4, kNG = 8;  // update / Gram warps
 constexpr int kMaxCB = 32;       // 8-column blocks (p <= 256)
 constexpr int kMaxNB = 4;        // tile buffers
-constexpr int kThreadsUG = (kNU + kNG + 1) * 32;
+constexpr int kThreadsUG = (kNU + kNG + 1) * 32;  // 13 warps, at most 4 per sub-partition: 128 registers per thread
 constexpr size_t kSmemUG = 224u << 10;
 
 struct UGArgs {
   double* V;
   const double* B;  // p x q, leading dimension ldb (device)
   int64_t ldv, n, ntiles;
-  int p, q, ldb, rows, nchunk, nbuf, dbg;
+  int p, q, ldb, rows, nchunk, nbuf;
   double alpha, beta;
   FusedDots fd;     // out[0 .. 2q): dot products, out[2q + k p + col]: (A^T V_new)(col, k)
 };
@@ -92,43 +92,76 @@ struct UGBars {
 // version unrolled to the maximum and predicated each slot on a run-time count: the chain ISETP -> @P LDS -> @P DMMA
 // through ONE predicate register serialised all 8 slots, ~280 cycles per 4-column step whatever the count --
 // 5x slower than the two separate kernels, profiles/r2_ug_predication_s8.txt.)
+//
+// One warp issues a DMMA every ~27 cycles at best (ncu: a fixed wait follows each one; the pipe of its
+// sub-partition takes one every 16), and a DMMA that accumulates onto the previous one of its chain waits for
+// it.  So: fragment loads in batches of K x N (one scoreboard wait per batch, not per DMMA), NCH
+// interleaved accumulator chains per row group, and a single-group warp (K = 1) takes two boxes per batch.
+template <int K, int N, int NCH>
+__device__ __forceinline__ void update_batch(double (&acc)[K][NCH][2], uint32_t a_addr, uint32_t b_addr,
+                                             uint32_t colstride, int chain0) {
+  double b[N], a[N][K];
+#pragma unroll
+  for (int ks = 0; ks < N; ++ks) b[ks] = lds_f64(b_addr + (uint32_t)(4 * ks) * 64u);
+#pragma unroll
+  for (int ks = 0; ks < N; ++ks)
+#pragma unroll
+    for (int i = 0; i < K; ++i) a[ks][i] = lds_f64(a_addr + (uint32_t)(4 * ks) * colstride + (uint32_t)(kNU * i) * 64u);
+#pragma unroll
+  for (int ks = 0; ks < N; ++ks)
+#pragma unroll
+    for (int i = 0; i < K; ++i)
+      B200_DMMA(acc[i][(chain0 + ks) % NCH][0], acc[i][(chain0 + ks) % NCH][1], a[ks][i], b[ks]);
+}
+
 template <int K>
 __device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UGBars& bar, unsigned char* xbuf0,
                                             unsigned char* tile0, const double* Bs, int64_t t_begin, int ntile_cta,
-                                            int warp, int lane, double (&dself)[2], double (&dold)[2]) {
+                                            int warp, int lane, double (*dred)[16]) {
+  // boxes per loop iteration / 4-column steps per batch: 16 DMMAs per batch where the registers allow it
+  constexpr int CS = K == 1 ? 4 : (K == 2 ? 2 : 1);
+  constexpr int NB = K <= 4 ? 4 : 2;  // steps per batch when a single box is processed (K x NB <= 16)
+  constexpr int NCH = K == 1 ? 4 : 2;
   const int R = u.rows, q = u.q, nchunk = u.nchunk;
   const uint32_t colstride = (uint32_t)R * 8u;
   // A fragment: lane l = (row l/4 of the group, basis column l%4 of the step); B: (k = l%4, n = l/4)
   const uint32_t a_lane = (uint32_t)(lane & 3) * colstride + (uint32_t)(lane >> 2) * 8u + (uint32_t)warp * 64u;
   const uint32_t b_addr = smem_u32(Bs) + (uint32_t)((lane & 3) * 8 + (lane >> 2)) * 8u;
   const int c0 = 2 * (lane & 3);  // this lane's output columns c0, c0 + 1
+  double dself[2] = {0.0, 0.0}, dold[2] = {0.0, 0.0};  // dot products of this lane's two columns
   int tb = 0;
   uint32_t par = 0;
   for (int t = 0; t < ntile_cta; ++t) {
     const int64_t r0 = (t_begin + t) * R;
-    double acc[K][2][2];
+    double acc[K][NCH][2];
 #pragma unroll
     for (int i = 0; i < K; ++i)
 #pragma unroll
-      for (int j = 0; j < 2; ++j) acc[i][0][j] = acc[i][1][j] = 0.0;
+      for (int h = 0; h < NCH; ++h) acc[i][h][0] = acc[i][h][1] = 0.0;
     const uint32_t tile_addr = smem_u32(tile0) + (uint32_t)tb * g.tile_bytes + a_lane;
-    for (int c = 0; c < nchunk; ++c) {
-      mbar_wait(&bar.full[tb][c], par);
-      if (u.dbg & 2) continue;
-      const uint32_t ch_addr = tile_addr + (uint32_t)c * g.chunk_bytes;
-      const uint32_t bc_addr = b_addr + (uint32_t)(c * kCW) * 64u;
-      // columns >= p of the last box are zero-filled by the TMA unit and meet zero rows of Bs: no column predicate
-      double b[kCW / 4];
+    // columns >= p of the last box are zero-filled by the TMA unit and meet zero rows of Bs: no column predicate
+    int c = 0;
+    for (; c + CS <= nchunk; c += CS) {
 #pragma unroll
-      for (int ks = 0; ks < kCW / 4; ++ks) b[ks] = lds_f64(bc_addr + (uint32_t)(4 * ks) * 64u);
+      for (int i = 0; i < CS; ++i) mbar_wait(&bar.full[tb][c + i], par);
+#ifndef B200_UG_NO_UPDATE
+      if (CS > 1) {
+        update_batch<K, 4 * CS, NCH>(acc, tile_addr + (uint32_t)(kCW * c) * colstride, b_addr + (uint32_t)(kCW * c) * 64u,
+                                     colstride, 0);
+      } else {
 #pragma unroll
-      for (int ks = 0; ks < kCW / 4; ++ks) {
-        double a[K];
-#pragma unroll
-        for (int i = 0; i < K; ++i) a[i] = lds_f64(ch_addr + (uint32_t)(4 * ks) * colstride + (uint32_t)(kNU * i) * 64u);
-#pragma unroll
-        for (int i = 0; i < K; ++i) B200_DMMA(acc[i][ks & 1][0], acc[i][ks & 1][1], a[i], b[ks]);
+        for (int h = 0; h < 4; h += NB)
+          update_batch<K, NB, NCH>(acc, tile_addr + (uint32_t)(kCW * c + 4 * h) * colstride,
+                                   b_addr + (uint32_t)(kCW * c + 4 * h) * 64u, colstride, 0);
       }
+#endif
+    }
+    for (; c < nchunk; ++c) {  // (CS > 1 only: boxes left over)
+      mbar_wait(&bar.full[tb][c], par);
+#ifndef B200_UG_NO_UPDATE
+      update_batch<K, 4, NCH>(acc, tile_addr + (uint32_t)(kCW * c) * colstride, b_addr + (uint32_t)(kCW * c) * 64u,
+                              colstride, 0);
+#endif
     }
     // C fragment: lane l holds rows l/4, columns 2 (l%4) + {0,1}.  The old X tile came with the first box
     // (rows >= n zero-filled); X_new replaces it in place, element by element, for the Gram warps.
@@ -140,7 +173,8 @@ __device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UG
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         if (c0 + j < q && rt < R) {
-          const double s = acc[i][0][j] + acc[i][1][j];
+          double s = acc[i][0][j] + acc[i][1][j];
+          if (NCH == 4) s += acc[i][2][j] + acc[i][3][j];
           double o;
           if (u.beta == 0.0) {
             o = row < u.n ? u.alpha * s : 0.0;
@@ -163,16 +197,50 @@ __device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UG
     }
     if (++tb == u.nbuf) { tb = 0; par ^= 1u; }
   }
+  // lanes with equal l%4 hold the same columns: fold over l/4
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    double a = dself[j], b = dold[j];
+#pragma unroll
+    for (int o = 4; o < 32; o <<= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    if (lane < 4) {
+      dred[warp][2 * (2 * lane + j)] = a;
+      dred[warp][2 * (2 * lane + j) + 1] = b;
+    }
+  }
+  // the arrivals that match the Gram warps' reduction rounds (gram_role)
+#pragma unroll
+  for (int round = 0; round <= kNG / 4; ++round) consumer_bar<(kNU + kNG) * 32>();
 }
 
 // ------------------------------------------------------------------ Gram warps
 // NCB = 8-column blocks of A (compile time: no predicated slots, see update_role).  Warp wg takes the 4-row steps
-// g = wg (mod 4) of every tile for all blocks; R / 4 = 8 K - 1 steps deal to 4 warps within one step of each other.
+// g = wg (mod 8) of every tile for all blocks.
 // Few blocks: two accumulator sets alternate by step, so that consecutive DMMAs of a block do not wait for each other.
+// one 4-row step (row = its byte offset in a column) against all NCB blocks, fragment loads in batches of 8
+template <int NCB, int NACC>
+__device__ __forceinline__ void gram_step(double (&acc)[NACC][2], uint32_t a_addr, uint32_t x_addr, uint32_t row,
+                                          uint32_t blk_stride, bool has_rhs) {
+  const double b = has_rhs ? lds_f64(x_addr + row) : 0.0;
+  constexpr int kB = NCB > 24 ? 4 : 8;  // (wide blocks: the accumulators leave fewer registers for the batch)
+#pragma unroll
+  for (int c0 = 0; c0 < NCB; c0 += kB) {
+    double a[kB];
+#pragma unroll
+    for (int cb = 0; cb < kB; ++cb)
+      if (c0 + cb < NCB) a[cb] = lds_f64(a_addr + row + (uint32_t)(c0 + cb) * blk_stride);
+#pragma unroll
+    for (int cb = 0; cb < kB; ++cb)
+      if (c0 + cb < NCB) B200_DMMA(acc[c0 + cb][0], acc[c0 + cb][1], a[cb], b);
+  }
+}
+
 template <int NCB>
 __device__ __forceinline__ void gram_role(const UGArgs& u, const UGSmem& g, UGBars& bar, unsigned char* xbuf0,
-                                          unsigned char* tile0, int ntile_cta, int wg, int lane,
-                                          double (&gacc)[kMaxCB][2]) {
+                                          unsigned char* tile0, int ntile_cta, int wg, int lane) {
   constexpr int NS = NCB <= 4 ? 2 : 1;
   const int R = u.rows, nchunk = u.nchunk;
   const int ng = R >> 2;
@@ -181,11 +249,11 @@ __device__ __forceinline__ void gram_role(const UGArgs& u, const UGSmem& g, UGBa
   const uint32_t frag = (uint32_t)(lane >> 2) * colstride + (uint32_t)(lane & 3) * 8u;
   const bool has_rhs = (lane >> 2) < u.q;
   const uint32_t blk_stride = 8u * colstride;
-  double acc[NS][NCB][2];
+  double gacc[NCB][2], acc1[NS == 2 ? NCB : 1][2];
 #pragma unroll
-  for (int s = 0; s < NS; ++s)
+  for (int cb = 0; cb < NCB; ++cb) gacc[cb][0] = gacc[cb][1] = 0.0;
 #pragma unroll
-    for (int cb = 0; cb < NCB; ++cb) acc[s][cb][0] = acc[s][cb][1] = 0.0;
+  for (int cb = 0; cb < (NS == 2 ? NCB : 1); ++cb) acc1[cb][0] = acc1[cb][1] = 0.0;
   int tb = 0;
   uint32_t par = 0;
   for (int t = 0; t < ntile_cta; ++t) {
@@ -193,38 +261,43 @@ __device__ __forceinline__ void gram_role(const UGArgs& u, const UGSmem& g, UGBa
     for (int c = 0; c < nchunk; ++c) mbar_wait(&bar.full[tb][c], par);  // (already complete: acquire of the TMA writes)
     const uint32_t a_addr = smem_u32(tile0) + (uint32_t)tb * g.tile_bytes + frag;
     const uint32_t x_addr = smem_u32(xbuf0) + (uint32_t)tb * g.x_bytes + frag;
-    if (!(u.dbg & 1)) {
+#ifndef B200_UG_NO_GRAM
+    {
       int g4 = wg;
-      for (; g4 + 4 * (NS - 1) < ng; g4 += 4 * NS) {
-#pragma unroll
-        for (int s = 0; s < NS; ++s) {
-          const uint32_t row = (uint32_t)(g4 + 4 * s) * 32u;  // 4 rows x 8 bytes
-          const double b = has_rhs ? lds_f64(x_addr + row) : 0.0;
-          double a[NCB];
-#pragma unroll
-          for (int cb = 0; cb < NCB; ++cb) a[cb] = lds_f64(a_addr + row + (uint32_t)cb * blk_stride);
-#pragma unroll
-          for (int cb = 0; cb < NCB; ++cb) B200_DMMA(acc[s][cb][0], acc[s][cb][1], a[cb], b);
-        }
+      for (; g4 + kNG * (NS - 1) < ng; g4 += kNG * NS) {
+        gram_step<NCB>(gacc, a_addr, x_addr, (uint32_t)g4 * 32u, blk_stride, has_rhs);
+        if (NS == 2) gram_step<NCB>(acc1, a_addr, x_addr, (uint32_t)(g4 + kNG) * 32u, blk_stride, has_rhs);
       }
-      if (NS == 2 && g4 < ng) {  // odd step left over
-        const uint32_t row = (uint32_t)g4 * 32u;
-        const double b = has_rhs ? lds_f64(x_addr + row) : 0.0;
-        double a[NCB];
-#pragma unroll
-        for (int cb = 0; cb < NCB; ++cb) a[cb] = lds_f64(a_addr + row + (uint32_t)cb * blk_stride);
-#pragma unroll
-        for (int cb = 0; cb < NCB; ++cb) B200_DMMA(acc[0][cb][0], acc[0][cb][1], a[cb], b);
-      }
+      if (NS == 2 && g4 < ng) gram_step<NCB>(gacc, a_addr, x_addr, (uint32_t)g4 * 32u, blk_stride, has_rhs);  // odd step left over
     }
+#endif
     __syncwarp();
     if (lane == 0) mbar_arrive(&bar.empty[tb]);
     if (++tb == u.nbuf) { tb = 0; par ^= 1u; }
   }
+  if (NS == 2) {
 #pragma unroll
-  for (int cb = 0; cb < NCB; ++cb) {
-    gacc[cb][0] = NS == 2 ? acc[0][cb][0] + acc[NS - 1][cb][0] : acc[0][cb][0];
-    gacc[cb][1] = NS == 2 ? acc[0][cb][1] + acc[NS - 1][cb][1] : acc[0][cb][1];
+    for (int cb = 0; cb < NCB; ++cb) {
+      gacc[cb][0] += acc1[cb][0];
+      gacc[cb][1] += acc1[cb][1];
+    }
+  }
+  // CTA partial of A^T V_new: the 8 Gram warps' blocks are summed in shared memory in two rounds of four warps (the
+  // tile buffers are free once every role has passed the first barrier; update_role makes the matching arrivals)
+  // C fragment: lane l holds (basis column 8 cb + l/4, right-hand sides 2 (l%4) + {0,1})
+  double* red = reinterpret_cast<double*>(tile0);  // [warp mod 4][8 NCB columns][8]
+  consumer_bar<(kNU + kNG) * 32>();
+#pragma unroll
+  for (int round = 0; round < kNG / 4; ++round) {
+    if ((wg >> 2) == round) {
+#pragma unroll
+      for (int cb = 0; cb < NCB; ++cb) {
+        double* r = red + ((size_t)((wg & 3) * NCB + cb) * 8 + (lane >> 2)) * 8 + 2 * (lane & 3);
+        r[0] = round == 0 ? gacc[cb][0] : r[0] + gacc[cb][0];
+        r[1] = round == 0 ? gacc[cb][1] : r[1] + gacc[cb][1];
+      }
+    }
+    consumer_bar<(kNU + kNG) * 32>();
   }
 }
 
@@ -232,13 +305,13 @@ __device__ __forceinline__ void gram_role(const UGArgs& u, const UGSmem& g, UGBa
 template <int LO, int HI>
 __device__ __forceinline__ void gram_dispatch(int ncb, const UGArgs& u, const UGSmem& g, UGBars& bar,
                                               unsigned char* xbuf0, unsigned char* tile0, int ntile_cta, int wg,
-                                              int lane, double (&gacc)[kMaxCB][2]) {
+                                              int lane) {
   if constexpr (LO == HI) {
-    gram_role<LO>(u, g, bar, xbuf0, tile0, ntile_cta, wg, lane, gacc);
+    gram_role<LO>(u, g, bar, xbuf0, tile0, ntile_cta, wg, lane);
   } else {
     constexpr int MID = (LO + HI) / 2;
-    if (ncb <= MID) gram_dispatch<LO, MID>(ncb, u, g, bar, xbuf0, tile0, ntile_cta, wg, lane, gacc);
-    else gram_dispatch<MID + 1, HI>(ncb, u, g, bar, xbuf0, tile0, ntile_cta, wg, lane, gacc);
+    if (ncb <= MID) gram_dispatch<LO, MID>(ncb, u, g, bar, xbuf0, tile0, ntile_cta, wg, lane);
+    else gram_dispatch<MID + 1, HI>(ncb, u, g, bar, xbuf0, tile0, ntile_cta, wg, lane);
   }
 }
 
@@ -275,12 +348,6 @@ __global__ void __launch_bounds__(kThreadsUG, 1)
   }
   __syncthreads();
 
-  double gacc[kMaxCB][2];      // Gram warps: (A^T V_new) blocks, kept over all tiles of the CTA
-  double dself[2], dold[2];    // update warps: dot products of this lane's two columns
-#pragma unroll
-  for (int i = 0; i < kMaxCB; ++i) gacc[i][0] = gacc[i][1] = 0.0;
-  dself[0] = dself[1] = dold[0] = dold[1] = 0.0;
-
   if (warp == kNU + kNG) {
     // ------------------------------------------------------------------ producer (one thread)
     if (lane == 0) {
@@ -304,52 +371,24 @@ __global__ void __launch_bounds__(kThreadsUG, 1)
     }
     __syncwarp();
   } else if (warp < kNU) {
-    switch ((R + 4) >> 5) {
-      case 1: update_role<1>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
-      case 2: update_role<2>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
-      case 3: update_role<3>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
-      case 4: update_role<4>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
-      case 5: update_role<5>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
-      case 6: update_role<6>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
-      case 7: update_role<7>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
-      default: update_role<8>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dself, dold); break;
+    switch ((R + 4) >> 5) {  // row groups per update warp
+      case 1: update_role<1>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred); break;
+      case 2: update_role<2>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred); break;
+      case 3: update_role<3>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred); break;
+      case 4: update_role<4>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred); break;
+      case 5: update_role<5>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred); break;
+      case 6: update_role<6>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred); break;
+      case 7: update_role<7>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred); break;
+      default: update_role<8>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred); break;
     }
   } else {
-    gram_dispatch<1, kMaxCB>((p + 7) >> 3, u, g, bar, xbuf0, tile0, ntile_cta, warp - kNU, lane, gacc);
+    gram_dispatch<1, kMaxCB>((p + 7) >> 3, u, g, bar, xbuf0, tile0, ntile_cta, warp - kNU, lane);
   }
+  __syncthreads();  // (the producer warp joins; the compute warps left their partials behind the named barrier)
 
-  // ---- CTA partials: Gram blocks of the 4 Gram warps through shared memory (the tile buffers are free:
-  // every load was consumed), dot products of the 4 update warps
-  __syncthreads();
+  // ---- CTA partials (the roles have left them in shared memory: red = the tile buffers, dred) -> workspace
   const int ncb8 = (p + 7) >> 3;
-  double* red = reinterpret_cast<double*>(tile0);  // [Gram warp][8 ncb8 columns][8]
-  if (warp >= kNU && warp < kNU + kNG) {
-    const int wg = warp - kNU;
-#pragma unroll
-    for (int cb = 0; cb < kMaxCB; ++cb) {
-      if (cb < ncb8) {
-        double* r = red + ((size_t)(wg * ncb8 + cb) * 8 + (lane >> 2)) * 8 + 2 * (lane & 3);
-        r[0] = gacc[cb][0];
-        r[1] = gacc[cb][1];
-      }
-    }
-  } else if (warp < kNU) {
-    // lanes with equal l%4 hold the same columns: fold over l/4
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      double a = dself[j], b = dold[j];
-#pragma unroll
-      for (int o = 4; o < 32; o <<= 1) {
-        a += __shfl_xor_sync(0xffffffffu, a, o);
-        b += __shfl_xor_sync(0xffffffffu, b, o);
-      }
-      if (lane < 4) {
-        dred[warp][2 * (2 * lane + j)] = a;
-        dred[warp][2 * (2 * lane + j) + 1] = b;
-      }
-    }
-  }
-  __syncthreads();
+  const double* red = reinterpret_cast<const double*>(tile0);
   const int ngram = p * q, nent = ngram + 2 * q;
   double* wsc = u.fd.ws + (size_t)blockIdx.x * nent;
   for (int e = threadIdx.x; e < nent; e += kThreadsUG) {
@@ -357,7 +396,7 @@ __global__ void __launch_bounds__(kThreadsUG, 1)
     if (e < ngram) {
       const int k = e / p, col = e - k * p;
 #pragma unroll
-      for (int w = 0; w < kNG; ++w) s += red[((size_t)w * ncb8 * 8 + col) * 8 + k];
+      for (int w = 0; w < 4; ++w) s += red[((size_t)w * ncb8 * 8 + col) * 8 + k];
     } else {
 #pragma unroll
       for (int w = 0; w < kNU; ++w) s += dred[w][e - ngram];
@@ -389,7 +428,7 @@ int ug_pick_rows(int p, int q, int64_t n, int num_sms) {
   int64_t cost[8];
   int cand[8];
   int nc = 0;
-  for (int R = 28; R <= 252; R += 32) {
+  for (int R = 28; R <= 252; R += 32) {  // 32 K - 4: the 8-row groups deal evenly to the 4 update warps
     if (ug_bufs(R, p, q) == 0) break;
     const int64_t nt = (n + R - 1) / R;
     const int64_t grid = std::min<int64_t>(num_sms, nt);
@@ -416,7 +455,8 @@ static int spec_mode() {  // B200_SPEC_GRAM: 0 never, 1 (default) when the call 
 // can launch_update_gram take this shape at all?
 bool update_gram_fits(Ctx* ctx, int p, int q, int64_t n) {
   if (spec_mode() == 0 || !ctx->fuse) return false;
-  if (p < 8 || p > kMaxCB * 8 || q < 1 || q > 8) return false;
+  // (below ~24 columns the two plain kernels are as fast: their fixed costs are smaller, profiles/r2_ug_sweep_s12.txt)
+  if (p < 24 || p > kMaxCB * 8 || q < 1 || q > 8) return false;
   if (n < (int64_t)ctx->num_sms * 28 * 4) return false;  // a few tiles per CTA, or the pipeline never fills
   return ug_pick_rows(p, q, n, ctx->num_sms) > 0;
 }
@@ -432,7 +472,6 @@ int launch_update_gram(Ctx* ctx, double* V, int64_t ldv, int q, const double* A,
   u.alpha = alpha; u.beta = beta; u.fd = fd;
   int R = ug_pick_rows(p, q, n, ctx->num_sms);
   if (const char* e = getenv("B200_UG_ROWS")) R = atoi(e);
-  u.dbg = getenv("B200_UG_DBG") ? atoi(getenv("B200_UG_DBG")) : 0;
   if (R <= 0) return fail(B200_ERR_ARG, "MvTimesMatAddMv: fused update + Gram does not fit (internal)");
   u.rows = R;
   u.nchunk = (p + kCW - 1) / kCW;
