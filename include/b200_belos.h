@@ -84,6 +84,11 @@ int b200_ctx_fusion_stats(const b200_ctx* ctx, int64_t* dot_hits);
  * hits = MvTransMv calls answered that way.  B200_SPEC_GRAM=0 in the environment disables it, =2 fuses every
  * eligible update (p <= 256 basis columns, <= 8 right-hand sides). */
 int b200_ctx_spec_gram_stats(const b200_ctx* ctx, int64_t* launches, int64_t* hits);
+/* findBasis column steps: the one-column MvTimesMatAddMv of DGKS findBasis also emits the products of
+ * the new column with the later columns of its block, and the block update before it the cross products of its columns,
+ * so that the one-column MvTransMv calls of the following column steps (belos/src/BelosDGKSOrthoManager.hpp:1064) are
+ * answered without a launch.  gram_calls_answered = such calls.  B200_FB_STEP=0 in the environment disables it. */
+int b200_ctx_findbasis_stats(const b200_ctx* ctx, int64_t* gram_calls_answered);
 /* Launches that never happened: single-column CloneCopy calls whose copy was made by the update kernel on its way
  * or was never needed (lazy copies), and single-column MvScale factors applied by the skinny Gram kernel that read
  * the column next (deferred scales).  DGKS findBasis makes one of each per column

@@ -589,3 +589,51 @@ def test_fused_update_gram_follows_the_two_pass_pattern(ctx):
         assert relerr(V.to_numpy(), v) <= 1e-12
     assert g1 - g0 >= steps - 2, "the second Gram of (almost) every step must come from the fused update"
     assert l1 - l0 <= steps + 3, "the second update of a step must stop speculating after the first steps"
+
+
+@pytest.mark.parametrize("n", [515, 20011, 100003])
+@pytest.mark.parametrize("b", [2, 4])
+def test_findbasis_after_block_update_needs_no_gram_launch(ctx, n, b):
+    """A whole block step as Belos::DGKSOrthoManager drives it: the second block update of blkOrtho
+    (BelosDGKSOrthoManager.hpp:1454), then findBasis column by column (:1000-1225).  The cross products of the block
+    update and of the column steps (findbasis.cu) answer every one-column MvTransMv: no Gram kernel runs, values as
+    the oracle's."""
+    p = 12
+    qb, x, c = rnd(n, p, 61), rnd(n, b, 62), rnd(p, b, 63) * 0.05
+    Q, X = tb.MultiVec.from_numpy(ctx, qb), tb.MultiVec.from_numpy(ctx, x)
+    ctx.set_fusion(True)
+    X.MvTimesMatAddMv(-1.0, Q, c, 1.0)
+    ref = oracle.times_mat_add_mv(-1.0, qb, c, 1.0, x)
+    h0 = ctx.findbasis_stats()
+    t0 = ctx.timing_read(reset=True)
+    ctx.timing_enable(True)
+    for j in range(b):
+        Xj = X.CloneViewNonConst([j])
+        old = Xj.CloneCopy() if j > 0 else None
+        old_dot = Xj.MvDot(Xj)
+        assert relerr(old_dot, oracle.dot(ref[:, [j]], ref[:, [j]])) <= TOL
+        if j > 0:
+            prev = X.CloneView(list(range(j)))
+            prod = Xj.MvTransMv(1.0, prev)
+            want = oracle.trans_mv(1.0, ref[:, :j], ref[:, [j]])
+            assert np.abs(prod - want).max() <= TOL * np.sqrt(old_dot[0]), (j, prod, want)  # (|prev_i| = 1)
+            refold = ref[:, [j]].copy()
+            Xj.MvTimesMatAddMv(-1.0, prev, prod, 1.0)
+            ref[:, [j]] = oracle.times_mat_add_mv(-1.0, ref[:, :j], prod, 1.0, ref[:, [j]])
+            new_dot = Xj.MvDot(Xj)
+            assert relerr(new_dot, oracle.dot(ref[:, [j]], ref[:, [j]])) <= TOL
+            od = Xj.MvDot(old)
+            assert np.abs(od - oracle.dot(ref[:, [j]], refold)).max() <= TOL * np.sqrt(new_dot * old_dot).max()
+            assert relerr(old.to_numpy(), refold) <= TOL, "the lazy copy must hold the column as it was"
+        else:
+            new_dot = old_dot
+        s = 1.0 / np.sqrt(new_dot[0])
+        Xj.MvScale(s)
+        ref[:, j] = ref[:, j] * s
+    ctx.timing_enable(False)
+    t = ctx.timing_read(reset=True)
+    assert ctx.findbasis_stats() - h0 == b - 1, "every one-column MvTransMv of the block step must come from the memo"
+    assert t["trans_mv"]["calls"] == 0 and t["dot_norm"]["calls"] == 0, t
+    assert relerr(X.to_numpy(), ref) <= TOL
+    g = oracle.trans_mv(1.0, X.to_numpy(), X.to_numpy())
+    assert np.abs(g - np.eye(b)).max() <= 1e-12

@@ -86,6 +86,12 @@ class Context:
         check(lib.b200_ctx_spec_gram_stats(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def findbasis_stats(self):
+        """one-column MvTransMv calls answered from remembered products (no launch)"""
+        a = c_i64()
+        check(lib.b200_ctx_findbasis_stats(self._h, C.byref(a)))
+        return a.value
+
     def deferral_stats(self):
         """(lazy single-column copies never launched, single-column scales folded into the next skinny Gram)"""
         a, b = c_i64(), c_i64()

@@ -426,7 +426,10 @@ extern "C" int b200_mv_scale(b200_mv* mv, double alpha) {
     B200_TRY(prep_write(mv, 0, 1, false));  // (copies of the unscaled column are made now; an older factor is applied)
     st->pscale[(size_t)c] = alpha;
     ++mv->ctx->pending;
+    const uint64_t before = mv->id(0);
     mv->touch(0, 1);
+    // products with this column that are already known (or on their way) stay known: x . y -> alpha (x . y)
+    mv->ctx->rescale_dots(before, mv->id(0), alpha);
     return 0;
   }
   B200_TRY(prep_write(mv, 0, mv->ncols(), false));
@@ -600,8 +603,22 @@ extern "C" int b200_mv_trans_mv(const b200_mv* mv, double alpha, const b200_mv* 
       }
     }
   }
-  // one vector against <= 8 columns (findBasis): the skinny kernel applies pending column scales itself and
-  // writes the scaled columns back -- the normalisation of the previous column costs no launch
+  // One vector against <= 8 columns (findBasis, BelosDGKSOrthoManager.hpp:1064): every entry may already be known --
+  // X0 . Xj from the cross products of the block update, Xi . Xj (i >= 1) from the column step of Xi (findbasis.cu).
+  if (ctx->fuse && q == 1 && p <= 8 && !A->st->external && !mv->st->external) {
+    double vals[8];
+    bool known = true;
+    int rc = 0;
+    for (int i = 0; i < p && known; ++i) known = ctx->recall_dot(A->id(i), mv->id(0), &vals[i], &rc);
+    if (rc) return rc;
+    if (known) {
+      for (int i = 0; i < p; ++i) B[i] = alpha * vals[i];
+      ++ctx->skinny_hits;
+      return 0;
+    }
+  }
+  // otherwise the skinny kernel: it applies pending column scales itself and writes the scaled columns back -- the
+  // normalisation of the previous column costs no launch
   double scales[9];
   bool fold = false;
   if (ctx->pending > 0 && gram_is_skinny(p, q) && run_length(0, p, A, 0) == p && mv->n_local > 0) {
@@ -668,6 +685,64 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
   }
   if (columns_overlap(mv, A))
     return fail(B200_ERR_ALIAS, "MvTimesMatAddMv: A and mv share columns (DGEMM forbids aliasing)");
+  // One column against <= 8 (a column step of findBasis): one kernel that also folds in the pending scales of A,
+  // fills a pending lazy copy of the target and leaves the dot products of the steps to come (findbasis.cu).
+  if (q == 1 && p <= 8 && ctx->fuse && fb_step_enabled() && run_length(0, p, A, 0) == p &&
+      !A->st->external && !mv->st->external && (ctx->nranks == 1 || ctx->p2p)) {
+    Storage* st = mv->st.get();
+    const int c = mv->cols[0];
+    B200_TRY(prep_read(A, 0, p, true));  // (pending copies INTO A's columns are made; their scales stay pending)
+    B200_TRY(lazy_materialize(st, c));
+    B200_TRY(scale_flush(st, c));
+    double* save_old = nullptr;
+    std::pair<Storage*, int> saved{nullptr, 0};
+    if (beta != 0.0 && st->deps[(size_t)c].size() == 1) {
+      saved = st->deps[(size_t)c][0];
+      save_old = saved.first->colptr(saved.second);
+    } else {
+      B200_TRY(deps_materialize(st, c));
+    }
+    double coef[8], scales[8];
+    for (int i = 0; i < p; ++i) {
+      coef[i] = B[i];
+      scales[i] = A->st->pscale[(size_t)A->cols[(size_t)i]];
+    }
+    // later columns of the block this column belongs to (the block the last multi-column update wrote)
+    int nx = 0;
+    if (ctx->last_block.st == st && c >= ctx->last_block.c0 && c < ctx->last_block.c0 + ctx->last_block.q) {
+      nx = std::min(7, ctx->last_block.c0 + ctx->last_block.q - 1 - c);
+      for (int k = 1; k <= nx; ++k)
+        if (st->lazy[(size_t)(c + k)].src || st->pscale[(size_t)(c + k)] != 1.0) nx = 0;  // (not plain data: skip)
+    }
+    FusedDots fd;
+    size_t src = 0;
+    if (!fused_slot(ctx, &fd, &src, 2 + nx)) return fail(B200_ERR_ARG, "MvTimesMatAddMv: no fused slot (internal)");
+    const uint64_t old_id = mv->id(0);
+    if (mv->n_local > 0)
+      B200_TRY(launch_fb_step(ctx, mv->col(0), A->col(0), A->ld, p, coef, scales, nx ? st->colptr(c + 1) : nullptr,
+                              st->ld, nx, mv->n_local, alpha, beta, save_old, fd));
+    else  // empty row block: this rank contributes zeros (and still joins the exchange)
+      B200_TRY(launch_zero_result(ctx, fd.out, 2 + nx, fd.pub));
+    mv->touch(0, 1);
+    for (int i = 0; i < p; ++i) {  // the kernel stored the scaled columns
+      Storage* sa = A->st.get();
+      const int ca = A->cols[(size_t)i];
+      if (sa->pscale[(size_t)ca] != 1.0) {
+        sa->pscale[(size_t)ca] = 1.0;
+        --ctx->pending;
+        ++ctx->scale_folded;
+      }
+    }
+    if (save_old) {  // the copy now holds the old column
+      lazy_unlink(saved.first, saved.second);
+      ++ctx->lazy_saved;
+    }
+    const uint64_t nid = mv->id(0);
+    ctx->remember_dot(nid, nid, 0.0, fd.seq, src);
+    if (beta != 0.0) ctx->remember_dot(nid, old_id, 0.0, fd.seq, src + 1);
+    for (int k = 0; k < nx; ++k) ctx->remember_dot(nid, st->ver[(size_t)(c + 1 + k)], 0.0, fd.seq, src + 2 + (size_t)k);
+    return 0;
+  }
   B200_TRY(prep_read(A));
   // One-column update whose target has exactly one pending lazy copy (findBasis: oldMXj): the kernel reads the old
   // values anyway and stores them into the copy on its way -- the CloneCopy launch never happens.
@@ -721,7 +796,12 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
            (size_t)p * q + 2 * (size_t)q <= (size_t)kSpecSlotDoubles &&
            fused_slot(ctx, &fd, &src, p * q + 2 * q, true);
   }
-  const bool fuse = spec || (plain && 2 * q <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src, 2 * q));
+  // q <= 4 through one SIMT launch: also the cross products new_i . new_k, the `product` entries of the findBasis
+  // column steps that follow (findbasis.cu)
+  // (q = 2 and q = 4 are single launches of the SIMT kernel; q = 3 is split 2 + 1)
+  const int ncross = (!spec && plain && (q == 2 || q == 4) && fb_step_enabled()) ? q * (q - 1) / 2 : 0;
+  const bool fuse = spec || (plain && 2 * q + ncross <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src, 2 * q + ncross));
+  if (fuse && !spec) fd.cross = ncross;
   std::vector<uint64_t> old_id(q);
   for (int j = 0; j < q; ++j) old_id[j] = mv->id(j);
   if (spec && mv->n_local > 0)
@@ -746,13 +826,23 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
     ++ctx->lazy_saved;
   }
   if (fuse && mv->n_local == 0)  // no kernel ran: the fused sums are zero, but must still be handed over
-    B200_TRY(launch_zero_result(ctx, fd.out, spec ? p * q + 2 * q : 2 * q, fd.pub));
+    B200_TRY(launch_zero_result(ctx, fd.out, spec ? p * q + 2 * q : 2 * q + ncross, fd.pub));
   if (fuse)
     for (int j = 0; j < q; ++j) {
       const uint64_t nid = mv->id(j);
       ctx->remember_dot(nid, nid, 0.0, fd.seq, src + 2 * j);
       if (beta != 0.0) ctx->remember_dot(nid, old_id[j], 0.0, fd.seq, src + 2 * j + 1);
     }
+  if (fuse && !spec && ncross) {
+    int e = 0;
+    for (int i = 0; i < q; ++i)
+      for (int k = i + 1; k < q; ++k, ++e) ctx->remember_dot(mv->id(i), mv->id(k), 0.0, fd.seq, src + 2 * (size_t)q + (size_t)e);
+  }
+  if (plain && q >= 2 && !mv->st->external) {
+    ctx->last_block.st = mv->st.get();
+    ctx->last_block.c0 = mv->cols[0];
+    ctx->last_block.q = q;
+  }
   if (eligible) {
     Ctx::SpecState& sp = ctx->spec;
     sp.a_ids.resize((size_t)p);

@@ -245,17 +245,17 @@ int Ctx::wait_flag(uint64_t s) {
 }
 
 // ------------------------------------------------------------------ remembered dot products
-void Ctx::remember_dot(uint64_t a, uint64_t b, double val, uint64_t seq_, size_t src) {
+void Ctx::remember_dot(uint64_t a, uint64_t b, double val, uint64_t seq_, size_t src, double mul) {
   if (!fuse) return;
   if (a > b) std::swap(a, b);
   for (int i = 0; i < kDotCache; ++i)
     if (dots[i].a == a && dots[i].b == b) {
-      dots[i].val = val; dots[i].seq = seq_; dots[i].src = src;
+      dots[i].val = val; dots[i].seq = seq_; dots[i].src = src; dots[i].mul = mul;
       return;
     }
   DotEntry& e = dots[dot_next];
   dot_next = (dot_next + 1) % kDotCache;
-  e.a = a; e.b = b; e.val = val; e.seq = seq_; e.src = src;
+  e.a = a; e.b = b; e.val = val; e.seq = seq_; e.src = src; e.mul = mul;
 }
 
 bool Ctx::recall_dot(uint64_t a, uint64_t b, double* val, int* rc) {
@@ -267,13 +267,31 @@ bool Ctx::recall_dot(uint64_t a, uint64_t b, double* val, int* rc) {
     if (e.seq != 0) {  // produced by a fused epilogue that may still be running
       *rc = wait_flag(e.seq);
       if (*rc) return false;
-      e.val = mbox_h[e.src];
+      e.val = e.mul * mbox_h[e.src];
       e.seq = 0;
+      e.mul = 1.0;
     }
     *val = e.val;
     return true;
   }
   return false;
+}
+
+void Ctx::rescale_dots(uint64_t from, uint64_t to, double factor) {
+  if (!fuse || from == 0) return;
+  DotEntry moved[16];
+  int nm = 0;
+  for (int i = 0; i < kDotCache && nm < 16; ++i) {
+    const DotEntry& e = dots[i];
+    if (e.a != from && e.b != from) continue;
+    DotEntry m = e;
+    const double f = (e.a == from && e.b == from) ? factor * factor : factor;
+    if (m.seq != 0) m.mul *= f; else m.val *= f;
+    if (m.a == from) m.a = to;
+    if (m.b == from) m.b = to;
+    moved[nm++] = m;
+  }
+  for (int i = 0; i < nm; ++i) remember_dot(moved[i].a, moved[i].b, moved[i].val, moved[i].seq, moved[i].src, moved[i].mul);
 }
 
 void Ctx::plan_reduction(int count, bool is_max) {
@@ -524,6 +542,7 @@ extern "C" int b200_ctx_set_fusion(b200_ctx* c, int on) {
   for (auto& e : c->dots) e = Ctx::DotEntry();
   c->gmemo.valid = false;
   c->spec = Ctx::SpecState();
+  c->last_block = Ctx::LastBlock();
   return 0;
 }
 
@@ -537,6 +556,12 @@ extern "C" int b200_ctx_spec_gram_stats(const b200_ctx* c, int64_t* launches, in
   if (!c) return fail(B200_ERR_ARG, "null context");
   if (launches) *launches = c->gram_spec;
   if (hits) *hits = c->gram_hits;
+  return 0;
+}
+
+extern "C" int b200_ctx_findbasis_stats(const b200_ctx* c, int64_t* gram_calls_answered) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  if (gram_calls_answered) *gram_calls_answered = c->skinny_hits;
   return 0;
 }
 

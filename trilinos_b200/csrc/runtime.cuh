@@ -25,7 +25,7 @@ constexpr int kStageSlots = 16;
 // Fused-reduction bookkeeping: kernels that write a column (SpMM, MvTimesMatAddMv) also emit the
 // column dot products Belos asks for next (x.x, x.x_old); the results wait in the upper part of
 // the host mailbox until the matching MvDot / MvNorm call picks them up without a launch.
-constexpr int kDotCache = 64;                   // remembered column dot products
+constexpr int kDotCache = 256;                  // remembered column dot products
 constexpr int kAuxSlots = 32;                   // mailbox slots for results of fused epilogues
 constexpr int kAuxSlotDoubles = 64;             // <= 32 columns x {self, with-old}
 constexpr size_t kAuxBase = kMailboxDoubles - (size_t)kAuxSlots * kAuxSlotDoubles;
@@ -92,6 +92,8 @@ struct FusedDots {
   // behind it.  Launches that are not the last one carry a default (inert) XchgPub.
   XchgPub pub;
   void not_last() { pub = XchgPub(); }
+  // multi-column update kernels (q <= 4): also emit new_i . new_k for i < k at out[2q + pair(i, k)]
+  int cross = 0;
 };
 
 enum KClass { K_SPMM = 0, K_GRAM = 1, K_UPDATE = 2, K_REDUCE = 3, K_AXPBY = 4, K_HALO = 5 };
@@ -143,8 +145,9 @@ struct Ctx {
   struct DotEntry {
     uint64_t a = 0, b = 0;    // content ids (a <= b)
     double val = 0.0;
-    uint64_t seq = 0;         // 0: val is final; else: published at mbox_h[src] once flag >= seq
+    uint64_t seq = 0;         // 0: val is final; else: mul * mbox_h[src], published once flag >= seq
     size_t src = 0;
+    double mul = 1.0;         // (a column that was scaled after the product was launched: deferred MvScale)
   };
   DotEntry dots[kDotCache];
   int dot_next = 0;
@@ -171,7 +174,15 @@ struct Ctx {
   } spec;
   int spec_next = 0;                     // next big slot
   int64_t gram_hits = 0, gram_spec = 0;  // memo answers / speculative launches (diagnostics)
-  void remember_dot(uint64_t a, uint64_t b, double val, uint64_t seq = 0, size_t src = 0);
+  void remember_dot(uint64_t a, uint64_t b, double val, uint64_t seq = 0, size_t src = 0, double mul = 1.0);
+  // column `from` was scaled by `factor` and is now known as `to`: its remembered products follow
+  void rescale_dots(uint64_t from, uint64_t to, double factor);
+  // the block the last multi-column MvTimesMatAddMv wrote (findBasis works through its columns next)
+  struct LastBlock {
+    const void* st = nullptr;
+    int c0 = 0, q = 0;
+  } last_block;
+  int64_t skinny_hits = 0;   // one-column MvTransMv calls answered from remembered products
   // true (and *val set, waiting for the producing kernel if needed) if the product is known
   bool recall_dot(uint64_t a, uint64_t b, double* val, int* rc);
   // counters / timing
@@ -411,6 +422,11 @@ bool gram_is_skinny(int p, int q);
 int launch_update(Ctx*, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
                   int64_t n, const double* dB, int ldb, double alpha, double beta,
                   const FusedDots* fused = nullptr, double* save_old = nullptr);
+// findbasis.cu : one-column update with pending scales, lazy copy, and dots with the later columns of the block
+bool fb_step_enabled();
+int launch_fb_step(Ctx*, double* x, double* A, int64_t lda, int p, const double* coef, const double* scale,
+                   const double* next, int64_t ldn, int nx, int64_t n, double alpha, double beta, double* save_old,
+                   const FusedDots& fd);
 // update_gram.cu : the same update; fused.out[0..2q) = the dot products, fused.out[2q + k p + col] = A^T V_new
 bool update_gram_fits(Ctx*, int p, int q, int64_t n);
 bool update_gram_always();

@@ -46,12 +46,16 @@ __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
   // once per CTA instead of once per wave of CTAs.
   const int64_t ntiles = (n + 4 * kThreads - 1) / (4 * kThreads);
   const bool single = p <= kPChunk;  // B fits one stage: load it once for all tiles
-  double dself[Q], dold[Q];
+  // cross products new_i . new_k (i < k), Q <= 4 only: the `product` entries findBasis asks for next (findbasis.cu)
+  constexpr int NX = (FUSE && Q >= 2 && Q <= 4) ? Q * (Q - 1) / 2 : 1;
+  double dself[Q], dold[Q], dcross[NX];
 #pragma unroll
   for (int k = 0; k < Q; ++k) {
     dself[k] = 0.0;
     dold[k] = 0.0;
   }
+#pragma unroll
+  for (int k = 0; k < NX; ++k) dcross[k] = 0.0;
   auto stage = [&](int j0, int pc) {
     for (int e = threadIdx.x; e < pc * Q; e += kThreads) {
       const int k = e / pc, j = e % pc;  // coalesced read of column k of B
@@ -111,6 +115,7 @@ __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
       }
     }
     if (active) {
+      double4v onew[(FUSE && Q >= 2 && Q <= 4) ? Q : 1];
 #pragma unroll
       for (int k = 0; k < Q; ++k) {
         double* vp = V + (size_t)k * ldv + r;
@@ -139,14 +144,30 @@ __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
           t0 = m2 ? fma(o.z, v.z, t0) : t0;
           t1 = m3 ? fma(o.w, v.w, t1) : t1;
           dold[k] += t0 + t1;
+          if (Q >= 2 && Q <= 4) {
+            onew[k].x = o.x; onew[k].y = m1 ? o.y : 0.0; onew[k].z = m2 ? o.z : 0.0; onew[k].w = m3 ? o.w : 0.0;
+          }
         }
+      }
+      if (FUSE && Q >= 2 && Q <= 4 && fd.cross) {
+        int e = 0;
+#pragma unroll
+        for (int i = 0; i < Q; ++i)
+#pragma unroll
+          for (int k = i + 1; k < Q; ++k, ++e) {
+            double t0 = onew[i].x * onew[k].x, t1 = onew[i].y * onew[k].y;
+            t0 = fma(onew[i].z, onew[k].z, t0);
+            t1 = fma(onew[i].w, onew[k].w, t1);
+            dcross[e] += t0 + t1;
+          }
       }
     }
   }
   if (!FUSE) return;
   // CTA partials -> workspace [entry][cta]; two-level deterministic fold, last CTA publishes
-  __shared__ double red[kThreads / 32][2 * Q];
+  __shared__ double red[kThreads / 32][2 * Q + NX];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nent = 2 * Q + ((Q >= 2 && Q <= 4 && fd.cross) ? NX : 0);
 #pragma unroll
   for (int k = 0; k < Q; ++k) {
     const double a = warp_sum(dself[k]), b = warp_sum(dold[k]);
@@ -155,14 +176,21 @@ __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
       red[warp][2 * k + 1] = b;
     }
   }
+  if (nent > 2 * Q) {
+#pragma unroll
+    for (int k = 0; k < NX; ++k) {
+      const double a = warp_sum(dcross[k]);
+      if (lane == 0) red[warp][2 * Q + k] = a;
+    }
+  }
   __syncthreads();
-  if (threadIdx.x < 2 * Q) {
+  if (threadIdx.x < nent) {
     double t = 0.0;
 #pragma unroll
     for (int w = 0; w < kThreads / 32; ++w) t += red[w][threadIdx.x];
     fd.ws[(size_t)threadIdx.x * gridDim.x + blockIdx.x] = t;
   }
-  if (!fold_partials_wide<kThreads / 32>(fd.ws, fd.ticket, 2 * Q, gridDim.x, blockIdx.x, 1, fd.out))
+  if (!fold_partials_wide<kThreads / 32>(fd.ws, fd.ticket, nent, gridDim.x, blockIdx.x, 1, fd.out))
     return;
   publish_result(fd.pub);
 }
@@ -467,6 +495,7 @@ int launch_update(Ctx* ctx, double* V, int64_t ldv, int q, const double* A, int6
       fd = *fused;
       fd.out = fused->out + 2 * k0;
       if (k0 + step < q) fd.not_last();  // only the last launch hands the results over
+      if (step != q || q > 4) fd.cross = 0;  // (the caller asks for cross products only where one SIMT launch covers q)
     }
     switch (step) {
       case 16: rc = launch_update_dmma<2>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
