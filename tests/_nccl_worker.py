@@ -53,6 +53,61 @@ def main():
         errs = dict(apply=e_apply, gram=e_gram, dot=e_dot, n2=e_n2, n1=e_n1, ninf=e_ni)
         assert max(errs.values()) <= TOL, (name, errs)
         out[name] = errs
+    # one block step of DGKS (BelosDGKSOrthoManager.hpp:1400-1472, :1000-1225) on row-partitioned random data, at a size where
+    # the fused update + Gram kernel and the findBasis memo are active: Gram, update (+ the next Gram from the mailbox),
+    # update (+ cross products), then the column steps -- every value against the serial oracle
+    from trilinos_b200.core import linear_partition
+    n, p, b = 18000 * world + 7, 40, 4
+    lo, hi = linear_partition(n, world, rank)
+    rng = np.random.default_rng(7)
+    qg = np.asfortranarray(rng.uniform(-1, 1, (n, p)))
+    Q = tb.MultiVec.from_numpy(ctx, qg[lo:hi], n_global=n, row_offset=lo)
+    ctx.set_fusion(True)
+    for rnd_ in range(2):  # (second round: the call-pattern predictor has learned that only the first update is followed by a Gram)
+        xg = np.asfortranarray(rng.uniform(-1, 1, (n, b)))
+        X = tb.MultiVec.from_numpy(ctx, xg[lo:hi], n_global=n, row_offset=lo)
+        s0, g0 = ctx.spec_gram_stats()
+        f0 = ctx.findbasis_stats()
+        errs = {}
+        c1 = X.MvTransMv(1.0, Q)
+        errs["gram1"] = rel(c1, oracle.trans_mv(1.0, qg, xg))
+        c1 = c1 * 1e-3
+        X.MvTimesMatAddMv(-1.0, Q, c1, 1.0)
+        xg = oracle.times_mat_add_mv(-1.0, qg, c1, 1.0, xg)
+        c2 = X.MvTransMv(1.0, Q)
+        errs["gram2_from_fused_update"] = rel(c2, oracle.trans_mv(1.0, qg, xg))
+        c2 = c2 * 1e-3
+        X.MvTimesMatAddMv(-1.0, Q, c2, 1.0)
+        xg = oracle.times_mat_add_mv(-1.0, qg, c2, 1.0, xg)
+        s1, g1 = ctx.spec_gram_stats()
+        assert g1 - g0 == 1, "the second Gram must have come from the fused update"
+        for j in range(b):
+            Xj = X.CloneViewNonConst([j])
+            old = Xj.CloneCopy() if j > 0 else None
+            d0 = Xj.MvDot(Xj)
+            errs[f"olddot{j}"] = rel(d0, oracle.dot(xg[:, [j]], xg[:, [j]]))
+            if j > 0:
+                prev = X.CloneView(list(range(j)))
+                prod = Xj.MvTransMv(1.0, prev)
+                want = oracle.trans_mv(1.0, xg[:, :j], xg[:, [j]])
+                errs[f"prod{j}"] = float(np.abs(prod - want).max() / np.sqrt(d0[0]))
+                Xj.MvTimesMatAddMv(-1.0, prev, prod, 1.0)
+                xg[:, [j]] = oracle.times_mat_add_mv(-1.0, xg[:, :j], prod, 1.0, xg[:, [j]])
+                d1 = Xj.MvDot(Xj)
+                errs[f"newdot{j}"] = rel(d1, oracle.dot(xg[:, [j]], xg[:, [j]]))
+                old.to_numpy()  # (a lazy copy that is read: filled by the column step)
+            else:
+                d1 = d0
+            sc = 1.0 / np.sqrt(d1[0])
+            Xj.MvScale(sc)
+            xg[:, j] *= sc
+        errs["x"] = rel(X.to_numpy(), xg[lo:hi])
+        assert max(errs.values()) <= TOL, errs
+        fb = ctx.findbasis_stats() - f0
+        if rnd_ == 1:
+            assert s1 - s0 == 1 and fb == b - 1, (s1 - s0, fb)
+        out[f"block_step_{rnd_}"] = dict(max_err=max(errs.values()), spec_launches=s1 - s0, gram_memo_hits=g1 - g0,
+                                         findbasis_hits=fb)
     # solves: iteration counts against the reference's golden runs (single-rank Epetra/Belos)
     for label, g in sorted(gold.items()):
         name, dims, b = g["matrix"], tuple(g["dims"]), g["block_size"]

@@ -709,8 +709,9 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
     }
     // later columns of the block this column belongs to (the block the last multi-column update wrote)
     int nx = 0;
-    if (ctx->last_block.st == st && c >= ctx->last_block.c0 && c < ctx->last_block.c0 + ctx->last_block.q) {
+    if (ctx->last_block.uid == st->uid && c >= ctx->last_block.c0 && c < ctx->last_block.c0 + ctx->last_block.q) {
       nx = std::min(7, ctx->last_block.c0 + ctx->last_block.q - 1 - c);
+      nx = std::max(0, std::min(nx, (int)st->ver.size() - 1 - c));
       for (int k = 1; k <= nx; ++k)
         if (st->lazy[(size_t)(c + k)].src || st->pscale[(size_t)(c + k)] != 1.0) nx = 0;  // (not plain data: skip)
     }
@@ -839,7 +840,7 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
       for (int k = i + 1; k < q; ++k, ++e) ctx->remember_dot(mv->id(i), mv->id(k), 0.0, fd.seq, src + 2 * (size_t)q + (size_t)e);
   }
   if (plain && q >= 2 && !mv->st->external) {
-    ctx->last_block.st = mv->st.get();
+    ctx->last_block.uid = mv->st->uid;
     ctx->last_block.c0 = mv->cols[0];
     ctx->last_block.q = q;
   }

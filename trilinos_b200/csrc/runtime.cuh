@@ -178,10 +178,13 @@ struct Ctx {
   // column `from` was scaled by `factor` and is now known as `to`: its remembered products follow
   void rescale_dots(uint64_t from, uint64_t to, double factor);
   // the block the last multi-column MvTimesMatAddMv wrote (findBasis works through its columns next)
+  // (identified by the storage's serial number, never by its address: a freed storage's address can be handed out
+  // again on one rank and not on another, and the ranks must take the same decisions)
   struct LastBlock {
-    const void* st = nullptr;
+    uint64_t uid = 0;
     int c0 = 0, q = 0;
   } last_block;
+  uint64_t next_uid = 1;
   int64_t skinny_hits = 0;   // one-column MvTransMv calls answered from remembered products
   // true (and *val set, waiting for the producing kernel if needed) if the product is known
   bool recall_dot(uint64_t a, uint64_t b, double* val, int* rc);
@@ -225,6 +228,7 @@ struct Storage {
   // writes a column gives it a fresh id; pure copies propagate the source id.
   std::vector<uint64_t> ver;
   bool external = false;  // a raw device pointer was handed out: contents are no longer tracked
+  uint64_t uid = 0;       // serial number of this storage within its context
   // Launch-bound single-column work of DGKS findBasis (BelosDGKSOrthoManager.hpp:1037, :1217-1222), kept
   // off the stream until something needs the data (capi.cu: prep_read / prep_write):
   //  * deferred MvScale of one column: its logical content is pscale[c] x the stored data; the skinny Gram
@@ -245,6 +249,7 @@ struct Storage {
       : ctx(c), ptr(p), bytes(b), ld(ld_), n_local(n_), ver((size_t)std::max(ncols, 1)),
         pscale((size_t)std::max(ncols, 1), 1.0), lazy((size_t)std::max(ncols, 1)), deps((size_t)std::max(ncols, 1)) {
     for (auto& v : ver) v = c->next_id++;
+    uid = c->next_uid++;
   }
   ~Storage();
   double* colptr(int c) const { return ptr + (size_t)c * ld; }
