@@ -89,14 +89,19 @@ int b200_ctx_spec_gram_stats(const b200_ctx* ctx, int64_t* launches, int64_t* hi
  * so that the one-column MvTransMv calls of the following column steps (belos/src/BelosDGKSOrthoManager.hpp:1064) are
  * answered without a launch.  gram_calls_answered = such calls.  B200_FB_STEP=0 in the environment disables it. */
 int b200_ctx_findbasis_stats(const b200_ctx* ctx, int64_t* gram_calls_answered);
+/* SURVEY 8(d) algorithmic bytes of the MvTransMv / MvDot / MvNorm calls that were answered from those memos, i.e.
+ * without a kernel of their own, since creation or the last reset (bench: whole-solve byte model). */
+int b200_ctx_answered_bytes(b200_ctx* ctx, double* bytes, int reset);
 /* Launches that never happened: single-column CloneCopy calls whose copy was made by the update kernel on its way
  * or was never needed (lazy copies), and single-column MvScale factors applied by the skinny Gram kernel that read
  * the column next (deferred scales).  DGKS findBasis makes one of each per column
  * (belos/src/BelosDGKSOrthoManager.hpp:1037, :1217-1222). */
 int b200_ctx_deferral_stats(const b200_ctx* ctx, int64_t* lazy_copies_saved, int64_t* scales_folded);
 /* per-kernel-class device timing (CUDA events on the compute stream).
- * classes: 0 spmm, 1 trans_mv, 2 times_mat_add_mv, 3 dot/norm, 4 axpby/scale/copy, 5 halo */
-#define B200_NUM_KCLASS 6
+ * classes: 0 spmm, 1 trans_mv, 2 times_mat_add_mv, 3 dot/norm, 4 axpby/scale/copy, 5 halo,
+ *          6 times_mat_add_mv fused with the next trans_mv (update_gram.cu; bytes = those of the update alone),
+ *          7 findBasis column step (findbasis.cu) */
+#define B200_NUM_KCLASS 8
 int b200_ctx_timing_enable(b200_ctx* ctx, int on);
 int b200_ctx_timing_read(b200_ctx* ctx, double* ms, int64_t* calls, double* bytes, int reset);
 /* raw stream handle (cudaStream_t) so a host harness can record its own events */

@@ -15,3 +15,6 @@ run python tools/ncu_ug.py 1000000 200 8
 run python tools/ncu_ug.py 125000 200 4
 run python tools/ncu_ug.py 125000 100 4
 cat $out
+out2=gpurun_out/r2_ug_sweep_s12_dmma.txt; : > $out2
+for p in 200 100 32; do echo "## DMMA update p=$p" >> $out2; B200_UG_DMMA_UPDATE=1 python tools/ncu_ug.py 1000000 $p 4 2>&1 | tail -1 >> $out2; done
+cat $out2

@@ -21,5 +21,6 @@ for _ in range(reps):
     ctx.flush_l2()
     X.MvTimesMatAddMv(-1.0, Q, Bm, 1.0)
 ctx.timing_enable(False)
-t = ctx.timing_read(reset=True)["times_mat_add_mv"]
+tr = ctx.timing_read(reset=True)
+t = tr["times_mat_add_mv_with_next_trans_mv"] if tr["times_mat_add_mv_with_next_trans_mv"]["calls"] else tr["times_mat_add_mv"]
 print(f"n={n} p={p} q={q}: {t['ms'] / t['calls'] * 1e3:.1f} us per update, spec launches/hits {ctx.spec_gram_stats()}")

@@ -53,6 +53,7 @@ _SIGS = {
     "b200_ctx_deferral_stats": (C.c_int, [vp, P(c_i64), P(c_i64)]),
     "b200_ctx_spec_gram_stats": (C.c_int, [vp, P(c_i64), P(c_i64)]),
     "b200_ctx_findbasis_stats": (C.c_int, [vp, P(c_i64)]),
+    "b200_ctx_answered_bytes": (C.c_int, [vp, P(c_dbl), C.c_int]),
     "b200_ctx_timing_enable": (C.c_int, [vp, C.c_int]),
     "b200_ctx_timing_read": (C.c_int, [vp, P(c_dbl), P(c_i64), P(c_dbl), C.c_int]),
     "b200_ctx_stream": (vp, [vp]),

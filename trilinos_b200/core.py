@@ -14,7 +14,8 @@ import numpy as np
 from ._lib import B200Error, check, lib, c_i32, c_i64, c_dbl, vp, P
 
 NORM_ONE, NORM_TWO, NORM_INF = 0, 1, 2
-KCLASS = ("spmm", "trans_mv", "times_mat_add_mv", "dot_norm", "axpby_scale_copy", "halo")
+KCLASS = ("spmm", "trans_mv", "times_mat_add_mv", "dot_norm", "axpby_scale_copy", "halo",
+          "times_mat_add_mv_with_next_trans_mv", "findbasis_column_step")
 
 
 def _dptr(a):
@@ -86,6 +87,12 @@ class Context:
         check(lib.b200_ctx_spec_gram_stats(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def answered_bytes(self, reset=True):
+        """SURVEY 8(d) bytes of the reduction calls answered from the memos (no kernel of their own)"""
+        a = c_dbl()
+        check(lib.b200_ctx_answered_bytes(self._h, C.byref(a), 1 if reset else 0))
+        return a.value
+
     def findbasis_stats(self):
         """one-column MvTransMv calls answered from remembered products (no launch)"""
         a = c_i64()
@@ -102,9 +109,9 @@ class Context:
         check(lib.b200_ctx_timing_enable(self._h, 1 if on else 0))
 
     def timing_read(self, reset=True):
-        ms = (c_dbl * 6)()
-        calls = (c_i64 * 6)()
-        nbytes = (c_dbl * 6)()
+        ms = (c_dbl * len(KCLASS))()
+        calls = (c_i64 * len(KCLASS))()
+        nbytes = (c_dbl * len(KCLASS))()
         check(lib.b200_ctx_timing_read(self._h, ms, calls, nbytes, 1 if reset else 0))
         return {k: {"ms": ms[i], "calls": calls[i], "bytes": nbytes[i]} for i, k in enumerate(KCLASS)}
 

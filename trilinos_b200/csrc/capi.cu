@@ -503,6 +503,7 @@ extern "C" int b200_mv_dot(const b200_mv* mv, const b200_mv* A, double* b, int n
   }
   if (known) {
     ctx->dot_hits += k;
+    ctx->answered_bytes += 8.0 * mv->n_local * k * (mv == A ? 1.0 : 2.0);
     return 0;
   }
   B200_TRY(prep_read(mv));
@@ -544,6 +545,7 @@ extern "C" int b200_mv_norm(const b200_mv* mv, int type, double* normvec, int nn
     }
     if (known) {
       ctx->dot_hits += k;
+      ctx->answered_bytes += 8.0 * mv->n_local * k;
       return 0;
     }
   }
@@ -599,6 +601,7 @@ extern "C" int b200_mv_trans_mv(const b200_mv* mv, double alpha, const b200_mv* 
         for (int j = 0; j < q; ++j)
           for (int i = 0; i < p; ++i) B[(size_t)j * ldb + i] = alpha * ctx->mbox_h[gm.src + (size_t)j * p + i];
         ++ctx->gram_hits;
+        ctx->answered_bytes += 8.0 * mv->n_local * ((double)p + q);
         return 0;
       }
     }
@@ -614,6 +617,7 @@ extern "C" int b200_mv_trans_mv(const b200_mv* mv, double alpha, const b200_mv* 
     if (known) {
       for (int i = 0; i < p; ++i) B[i] = alpha * vals[i];
       ++ctx->skinny_hits;
+      ctx->answered_bytes += 8.0 * mv->n_local * ((double)p + 1.0);
       return 0;
     }
   }

@@ -167,7 +167,7 @@ int launch_fb_step(Ctx* ctx, double* x, double* A, int64_t lda, int p, const dou
     if (f.scale[j] != 1.0) f.any_scale = 1;
   }
   f.alpha = alpha; f.beta = beta; f.fd = fd;
-  ctx->t_begin(K_UPDATE, 8.0 * n * ((double)p + (beta == 0.0 ? 1.0 : 2.0)));
+  ctx->t_begin(K_FBSTEP, 8.0 * n * ((double)p + (beta == 0.0 ? 1.0 : 2.0)));
   int rc;
   if (p <= 4 && nx <= 3) rc = launch_fb_t<4, 3>(ctx, f);
   else rc = launch_fb_t<8, 7>(ctx, f);

@@ -559,6 +559,13 @@ extern "C" int b200_ctx_spec_gram_stats(const b200_ctx* c, int64_t* launches, in
   return 0;
 }
 
+extern "C" int b200_ctx_answered_bytes(b200_ctx* c, double* bytes, int reset) {
+  if (!c) return fail(B200_ERR_ARG, "null context");
+  if (bytes) *bytes = c->answered_bytes;
+  if (reset) c->answered_bytes = 0.0;
+  return 0;
+}
+
 extern "C" int b200_ctx_findbasis_stats(const b200_ctx* c, int64_t* gram_calls_answered) {
   if (!c) return fail(B200_ERR_ARG, "null context");
   if (gram_calls_answered) *gram_calls_answered = c->skinny_hits;

@@ -96,7 +96,7 @@ struct FusedDots {
   int cross = 0;
 };
 
-enum KClass { K_SPMM = 0, K_GRAM = 1, K_UPDATE = 2, K_REDUCE = 3, K_AXPBY = 4, K_HALO = 5 };
+enum KClass { K_SPMM = 0, K_GRAM = 1, K_UPDATE = 2, K_REDUCE = 3, K_AXPBY = 4, K_HALO = 5, K_UPDATE_GRAM = 6, K_FBSTEP = 7 };
 
 struct Ctx {
   int device = 0;
@@ -186,6 +186,7 @@ struct Ctx {
   } last_block;
   uint64_t next_uid = 1;
   int64_t skinny_hits = 0;   // one-column MvTransMv calls answered from remembered products
+  double answered_bytes = 0.0;  // SURVEY 8(d) bytes of the calls that were answered without a kernel (memos)
   // true (and *val set, waiting for the producing kernel if needed) if the product is known
   bool recall_dot(uint64_t a, uint64_t b, double* val, int* rc);
   // counters / timing

@@ -54,6 +54,7 @@ constexpr int kMaxChunks = 16;   // p <= 256
 constexpr int kNU = 4, kNG = 8;  // update / Gram warps
 constexpr int kMaxCB = 32;       // 8-column blocks (p <= 256)
 constexpr int kMaxNB = 4;        // tile buffers
+constexpr int kGC = 4;           // boxes per release group: a buffer is refilled 64 columns at a time, as the Gram sweep leaves them
 constexpr int kThreadsUG = (kNU + kNG + 1) * 32;  // 13 warps, at most 4 per sub-partition: 128 registers per thread
 constexpr size_t kSmemUG = 224u << 10;
 
@@ -61,7 +62,7 @@ struct UGArgs {
   double* V;
   const double* B;  // p x q, leading dimension ldb (device)
   int64_t ldv, n, ntiles;
-  int p, q, ldb, rows, nchunk, nbuf;
+  int p, q, ldb, rows, nchunk, nbuf, dmma_update;
   double alpha, beta;
   FusedDots fd;     // out[0 .. 2q): dot products, out[2q + k p + col]: (A^T V_new)(col, k)
 };
@@ -79,7 +80,7 @@ struct UGSmem {
 };
 
 struct UGBars {
-  uint64_t full[kMaxNB][kMaxChunks], empty[kMaxNB], xfull[kMaxNB];
+  uint64_t full[kMaxNB][kMaxChunks], gempty[kMaxNB][kMaxChunks / kGC], xfull[kMaxNB];
 };
 
 #define B200_DMMA(c0, c1, a, b)                                                                \
@@ -140,6 +141,8 @@ __device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UG
       for (int h = 0; h < NCH; ++h) acc[i][h][0] = acc[i][h][1] = 0.0;
     const uint32_t tile_addr = smem_u32(tile0) + (uint32_t)tb * g.tile_bytes + a_lane;
     // columns >= p of the last box are zero-filled by the TMA unit and meet zero rows of Bs: no column predicate
+    // (a release group of kGC boxes is handed back as soon as this warp has read it -- except the last one, which
+    // goes with the tile's X buffer at the end)
     int c = 0;
     for (; c + CS <= nchunk; c += CS) {
 #pragma unroll
@@ -155,6 +158,10 @@ __device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UG
                                    b_addr + (uint32_t)(kCW * c + 4 * h) * 64u, colstride, 0);
       }
 #endif
+      if (((c + CS) & (kGC - 1)) == 0 && c + CS < nchunk) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar.gempty[tb][(c + CS) / kGC - 1]);
+      }
     }
     for (; c < nchunk; ++c) {  // (CS > 1 only: boxes left over)
       mbar_wait(&bar.full[tb][c], par);
@@ -162,8 +169,12 @@ __device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UG
       update_batch<K, 4, NCH>(acc, tile_addr + (uint32_t)(kCW * c) * colstride, b_addr + (uint32_t)(kCW * c) * 64u,
                               colstride, 0);
 #endif
+      if (((c + 1) & (kGC - 1)) == 0 && c + 1 < nchunk) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar.gempty[tb][(c + 1) / kGC - 1]);
+      }
     }
-    // C fragment: lane l holds rows l/4, columns 2 (l%4) + {0,1}.  The old X tile came with the first box
+    // C fragment: lane l holds rows l/4, columns 2 (l%4) + {0,1}.  The old X tile came with the last box
     // (rows >= n zero-filled); X_new replaces it in place, element by element, for the Gram warps.
     double* xb = reinterpret_cast<double*>(xbuf0 + (size_t)tb * g.x_bytes);
 #pragma unroll
@@ -193,7 +204,7 @@ __device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UG
     __syncwarp();
     if (lane == 0) {
       mbar_arrive(&bar.xfull[tb]);
-      mbar_arrive(&bar.empty[tb]);
+      mbar_arrive(&bar.gempty[tb][(nchunk - 1) / kGC]);
     }
     if (++tb == u.nbuf) { tb = 0; par ^= 1u; }
   }
@@ -216,33 +227,164 @@ __device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UG
   for (int round = 0; round <= kNG / 4; ++round) consumer_bar<(kNU + kNG) * 32>();
 }
 
+// ------------------------------------------------------------------ update warps, q <= 4: SIMT
+// With at most 4 right-hand sides half of every update DMMA is padding (N = 8), and a warp issues a DMMA only every
+// ~27 cycles: 128 useful FMAs per 27 issue cycles.  Plain DFMA does 32 FMAs per instruction: the 4 update warps then
+// need ~1/3 of the issue time (and the FP64 pipe sees half the work), and stop being the role the tile waits for
+// (ncu, profiles/r2_ug_ncu_s13.txt: update warps busy 85 % with the DMMA version).
+//   NH = 2 (R <= 64):  lane = 16 h + (row mod 16): the two halves of a warp take the even / odd columns of the same 16
+//                      rows (two 128-byte runs per load: conflict-free), partial sums meet by one shuffle;
+//   NH = 1:            lane = row mod 32, RP = 1 (R <= 128) or 2 rows per lane (row, row + 128).
+// B comes as warp-wide broadcasts from the zero-padded [column][8] copy, so all 4 accumulators are always computed.
+__device__ __forceinline__ void lds_b4(uint32_t addr, double (&b)[4]) {
+  asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(b[0]), "=d"(b[1]) : "r"(addr));
+  asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(b[2]), "=d"(b[3]) : "r"(addr + 16u));
+}
+
+template <int NH, int RP>
+__device__ __forceinline__ void update_role_simt(const UGArgs& u, const UGSmem& g, UGBars& bar, unsigned char* xbuf0,
+                                                 unsigned char* tile0, const double* Bs, int64_t t_begin,
+                                                 int ntile_cta, int warp, int lane, double (*dred)[16]) {
+  const int R = u.rows, q = u.q, nchunk = u.nchunk;
+  const uint32_t colstride = (uint32_t)R * 8u;
+  const int h = NH == 2 ? lane >> 4 : 0;
+  int rowt[RP];
+  rowt[0] = NH == 2 ? 16 * warp + (lane & 15) : 32 * warp + lane;
+  if (RP == 2) rowt[RP - 1] = rowt[0] + 128;
+  uint32_t a_off[RP];
+#pragma unroll
+  for (int i = 0; i < RP; ++i) a_off[i] = (uint32_t)min(rowt[i], R - 1) * 8u + (uint32_t)h * colstride;  // (rows >= R: clamped, not stored)
+  const uint32_t b_addr = smem_u32(Bs) + (uint32_t)h * 64u;
+  double dself[4] = {0.0, 0.0, 0.0, 0.0}, dold[4] = {0.0, 0.0, 0.0, 0.0};
+  int tb = 0;
+  uint32_t par = 0;
+  for (int t = 0; t < ntile_cta; ++t) {
+    const int64_t r0 = (t_begin + t) * R;
+    double acc[RP][4];
+#pragma unroll
+    for (int i = 0; i < RP; ++i)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc[i][c] = 0.0;
+    const uint32_t tile_addr = smem_u32(tile0) + (uint32_t)tb * g.tile_bytes;
+    for (int cch = 0; cch < nchunk; ++cch) {
+      mbar_wait(&bar.full[tb][cch], par);
+#ifndef B200_UG_NO_UPDATE
+      const uint32_t ca = tile_addr + (uint32_t)(kCW * cch) * colstride, cb = b_addr + (uint32_t)(kCW * cch) * 64u;
+      constexpr int CPC = kCW / NH;  // columns of a box per lane
+      double a[CPC][RP];
+#pragma unroll
+      for (int jj = 0; jj < CPC; ++jj)
+#pragma unroll
+        for (int i = 0; i < RP; ++i) a[jj][i] = lds_f64(ca + (uint32_t)(NH * jj) * colstride + a_off[i]);
+#pragma unroll
+      for (int jj = 0; jj < CPC; ++jj) {
+        double b[4];
+        lds_b4(cb + (uint32_t)(NH * jj) * 64u, b);
+#pragma unroll
+        for (int i = 0; i < RP; ++i)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) acc[i][c] = fma(a[jj][i], b[c], acc[i][c]);
+      }
+#endif
+      if (((cch + 1) & (kGC - 1)) == 0 && cch + 1 < nchunk) {  // a release group handed back (the last one: with the X buffer)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar.gempty[tb][(cch + 1) / kGC - 1]);
+      }
+    }
+    if (NH == 2) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc[0][c] += __shfl_xor_sync(0xffffffffu, acc[0][c], 16);
+    }
+    // The old X tile came with the last box (rows >= n zero-filled); X_new replaces it in place for the Gram warps.
+    double* xb = reinterpret_cast<double*>(xbuf0 + (size_t)tb * g.x_bytes);
+#pragma unroll
+    for (int i = 0; i < RP; ++i) {
+      const int rt = rowt[i];
+      const int64_t row = r0 + rt;
+      if (rt < R && h == 0) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (c < q) {
+            const double s = acc[i][c];
+            double o;
+            if (u.beta == 0.0) {
+              o = row < u.n ? u.alpha * s : 0.0;
+              dself[c] = fma(o, o, dself[c]);
+            } else {
+              const double v = xb[c * R + rt];
+              o = fma(u.alpha, s, u.beta * v);
+              dself[c] = fma(o, o, dself[c]);
+              dold[c] = fma(o, v, dold[c]);
+            }
+            if (row < u.n) u.V[(size_t)c * u.ldv + row] = o;
+            xb[c * R + rt] = o;
+          }
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) {
+      mbar_arrive(&bar.xfull[tb]);
+      mbar_arrive(&bar.gempty[tb][(nchunk - 1) / kGC]);
+    }
+    if (++tb == u.nbuf) { tb = 0; par ^= 1u; }
+  }
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const double a = warp_sum(dself[c]), b = warp_sum(dold[c]);
+    if (lane == 0) {
+      dred[warp][2 * c] = a;
+      dred[warp][2 * c + 1] = b;
+    }
+  }
+  if (lane < 8) dred[warp][8 + lane] = 0.0;  // (columns 4..7 do not exist on this path)
+  // the arrivals that match the Gram warps' reduction rounds (gram_role)
+#pragma unroll
+  for (int round = 0; round <= kNG / 4; ++round) consumer_bar<(kNU + kNG) * 32>();
+}
+
 // ------------------------------------------------------------------ Gram warps
 // NCB = 8-column blocks of A (compile time: no predicated slots, see update_role).  Warp wg takes the 4-row steps
 // g = wg (mod 8) of every tile for all blocks.
 // Few blocks: two accumulator sets alternate by step, so that consecutive DMMAs of a block do not wait for each other.
-// one 4-row step (row = its byte offset in a column) against all NCB blocks, fragment loads in batches of 8
-template <int NCB, int NACC>
+// one 4-row step (row = its byte offset in a column) against the blocks [C0, C0 + N) of A: N fragment loads, N DMMAs
+template <int C0, int N, int NACC>
 __device__ __forceinline__ void gram_step(double (&acc)[NACC][2], uint32_t a_addr, uint32_t x_addr, uint32_t row,
                                           uint32_t blk_stride, bool has_rhs) {
   const double b = has_rhs ? lds_f64(x_addr + row) : 0.0;
-  constexpr int kB = NCB > 24 ? 4 : 8;  // (wide blocks: the accumulators leave fewer registers for the batch)
+  double a[N];
 #pragma unroll
-  for (int c0 = 0; c0 < NCB; c0 += kB) {
-    double a[kB];
+  for (int cb = 0; cb < N; ++cb) a[cb] = lds_f64(a_addr + row + (uint32_t)(C0 + cb) * blk_stride);
 #pragma unroll
-    for (int cb = 0; cb < kB; ++cb)
-      if (c0 + cb < NCB) a[cb] = lds_f64(a_addr + row + (uint32_t)(c0 + cb) * blk_stride);
-#pragma unroll
-    for (int cb = 0; cb < kB; ++cb)
-      if (c0 + cb < NCB) B200_DMMA(acc[c0 + cb][0], acc[c0 + cb][1], a[cb], b);
-  }
+  for (int cb = 0; cb < N; ++cb) B200_DMMA(acc[C0 + cb][0], acc[C0 + cb][1], a[cb], b);
 }
 
+// the sweep of one tile over release group GRP (8 blocks = kGC boxes), then the groups after it
+template <int NCB, int GRP>
+__device__ __forceinline__ void gram_groups(double (&gacc)[NCB][2], double (&acc1)[NCB <= 4 ? NCB : 1][2], UGBars& bar, int tb,
+                                            uint32_t a_addr, uint32_t x_addr, uint32_t blk_stride, bool has_rhs, int ng,
+                                            int wg, int lane) {
+  constexpr int C0 = 8 * GRP, N = NCB - C0 < 8 ? NCB - C0 : 8, NS = NCB <= 4 ? 2 : 1;
+  int g4 = wg;
+  for (; g4 + kNG * (NS - 1) < ng; g4 += kNG * NS) {
+    gram_step<C0, N>(gacc, a_addr, x_addr, (uint32_t)g4 * 32u, blk_stride, has_rhs);
+    if constexpr (NS == 2) gram_step<C0, N>(acc1, a_addr, x_addr, (uint32_t)(g4 + kNG) * 32u, blk_stride, has_rhs);
+  }
+  if (NS == 2 && g4 < ng) gram_step<C0, N>(gacc, a_addr, x_addr, (uint32_t)g4 * 32u, blk_stride, has_rhs);  // odd step left over
+  __syncwarp();
+  if (lane == 0) mbar_arrive(&bar.gempty[tb][GRP]);  // (the last group also releases the tile's X buffer)
+  if constexpr (C0 + 8 < NCB) gram_groups<NCB, GRP + 1>(gacc, acc1, bar, tb, a_addr, x_addr, blk_stride, has_rhs, ng, wg, lane);
+}
+
+// NCB = 8-column blocks of A (compile time: no predicated slots, see update_role).  Warp wg takes the 4-row steps
+// g = wg (mod 8) of every tile, release group by release group (64 columns: 8 independent accumulator chains), so the
+// producer refills a buffer while the sweep is still on its later columns.
+// Few blocks: two accumulator sets alternate by step, so that consecutive DMMAs of a block do not wait for each other.
 template <int NCB>
 __device__ __forceinline__ void gram_role(const UGArgs& u, const UGSmem& g, UGBars& bar, unsigned char* xbuf0,
                                           unsigned char* tile0, int ntile_cta, int wg, int lane) {
   constexpr int NS = NCB <= 4 ? 2 : 1;
-  const int R = u.rows, nchunk = u.nchunk;
+  const int R = u.rows;
   const int ng = R >> 2;
   const uint32_t colstride = (uint32_t)R * 8u;
   // A^T fragment: lane l = (basis column l/4 of the block, row l%4 of the step); V_new: (k = l%4, n = l/4)
@@ -257,22 +399,17 @@ __device__ __forceinline__ void gram_role(const UGArgs& u, const UGSmem& g, UGBa
   int tb = 0;
   uint32_t par = 0;
   for (int t = 0; t < ntile_cta; ++t) {
+    // X_new complete: every update warp has waited for every box of the tile before it arrived here, so the boxes
+    // are complete and (acquire through this barrier) visible
     mbar_wait(&bar.xfull[tb], par);
-    for (int c = 0; c < nchunk; ++c) mbar_wait(&bar.full[tb][c], par);  // (already complete: acquire of the TMA writes)
     const uint32_t a_addr = smem_u32(tile0) + (uint32_t)tb * g.tile_bytes + frag;
     const uint32_t x_addr = smem_u32(xbuf0) + (uint32_t)tb * g.x_bytes + frag;
 #ifndef B200_UG_NO_GRAM
-    {
-      int g4 = wg;
-      for (; g4 + kNG * (NS - 1) < ng; g4 += kNG * NS) {
-        gram_step<NCB>(gacc, a_addr, x_addr, (uint32_t)g4 * 32u, blk_stride, has_rhs);
-        if (NS == 2) gram_step<NCB>(acc1, a_addr, x_addr, (uint32_t)(g4 + kNG) * 32u, blk_stride, has_rhs);
-      }
-      if (NS == 2 && g4 < ng) gram_step<NCB>(gacc, a_addr, x_addr, (uint32_t)g4 * 32u, blk_stride, has_rhs);  // odd step left over
-    }
-#endif
+    gram_groups<NCB, 0>(gacc, acc1, bar, tb, a_addr, x_addr, blk_stride, has_rhs, ng, wg, lane);
+#else
     __syncwarp();
-    if (lane == 0) mbar_arrive(&bar.empty[tb]);
+    if (lane == 0) for (int grp = 0; grp <= (u.nchunk - 1) / kGC; ++grp) mbar_arrive(&bar.gempty[tb][grp]);
+#endif
     if (++tb == u.nbuf) { tb = 0; par ^= 1u; }
   }
   if (NS == 2) {
@@ -341,7 +478,7 @@ __global__ void __launch_bounds__(kThreadsUG, 1)
   if (threadIdx.x == 0) {
     for (int b = 0; b < u.nbuf; ++b) {
       for (int c = 0; c < nchunk; ++c) mbar_init(&bar.full[b][c], 1);
-      mbar_init(&bar.empty[b], kNU + kNG);
+      for (int c = 0; c < kMaxChunks / kGC; ++c) mbar_init(&bar.gempty[b][c], kNU + kNG);
       mbar_init(&bar.xfull[b], kNU);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -356,12 +493,13 @@ __global__ void __launch_bounds__(kThreadsUG, 1)
       int tb = 0;
       uint32_t par = 0;
       for (int t = 0; t < ntile_cta; ++t) {
-        mbar_wait(&bar.empty[tb], par ^ 1u);
         const int r0 = (int)((t_begin + t) * R);
         unsigned char* dst = tile0 + (size_t)tb * g.tile_bytes;
         for (int c = 0; c < nchunk; ++c) {
-          // the old X tile (beta != 0) travels with the first box: [column][R], the layout X_new is left in
-          const bool with_x = c == 0 && u.beta != 0.0;
+          if ((c & (kGC - 1)) == 0) mbar_wait(&bar.gempty[tb][c / kGC], par ^ 1u);  // both roles are done with this group
+          // the old X tile (beta != 0) travels with the LAST box (its buffer is released with the last group):
+          // [column][R], the layout X_new is left in
+          const bool with_x = c == nchunk - 1 && u.beta != 0.0;
           mbar_expect_tx(&bar.full[tb][c], g.chunk_bytes + (with_x ? (uint32_t)(q * R) * 8u : 0u));
           tma_load_2d(dst + (size_t)c * g.chunk_bytes, &tmA, r0, c * kCW, &bar.full[tb][c], pol);
           if (with_x) tma_load_2d(xbuf0 + (size_t)tb * g.x_bytes, &tmV, r0, 0, &bar.full[tb][c], pol_v);
@@ -370,6 +508,10 @@ __global__ void __launch_bounds__(kThreadsUG, 1)
       }
     }
     __syncwarp();
+  } else if (warp < kNU && q <= 4 && !u.dmma_update) {
+    if (R <= 64) update_role_simt<2, 1>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred);
+    else if (R <= 128) update_role_simt<1, 1>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred);
+    else update_role_simt<1, 2>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred);
   } else if (warp < kNU) {
     switch ((R + 4) >> 5) {  // row groups per update warp
       case 1: update_role<1>(u, g, bar, xbuf0, tile0, Bs, t_begin, ntile_cta, warp, lane, dred); break;
@@ -476,6 +618,9 @@ int launch_update_gram(Ctx* ctx, double* V, int64_t ldv, int q, const double* A,
   u.rows = R;
   u.nchunk = (p + kCW - 1) / kCW;
   u.nbuf = ug_bufs(R, p, q);
+  // q <= 4: the SIMT update role up to 80 basis columns, the DMMA one beyond (measured cross-over, 1M rows: p = 64
+  // 122 vs 142 us, p = 100 214 vs 204 us, p = 200 373 vs 336 us; profiles/r2_ug_roles_s19.txt).  B200_UG_DMMA_UPDATE=0/1 forces one.
+  u.dmma_update = getenv("B200_UG_DMMA_UPDATE") ? atoi(getenv("B200_UG_DMMA_UPDATE")) : (p > 80 ? 1 : 0);
   if (const char* e = getenv("B200_UG_BUFS")) u.nbuf = std::max(2, std::min(u.nbuf, atoi(e)));
   if (u.nbuf < 2 || R % 32 != 28 || R > 252)
     return fail(B200_ERR_ARG, "MvTimesMatAddMv: fused update + Gram: bad tile height (internal)");
@@ -493,7 +638,7 @@ int launch_update_gram(Ctx* ctx, double* V, int64_t ldv, int q, const double* A,
                                    (int)kSmemUG));
     attr_devs |= 1u << (ctx->device & 31);
   }
-  ctx->t_begin(K_UPDATE, 8.0 * n * ((double)p + (beta == 0.0 ? 1.0 : 2.0) * q));
+  ctx->t_begin(K_UPDATE_GRAM, 8.0 * n * ((double)p + (beta == 0.0 ? 1.0 : 2.0) * q));
   update_gram_kernel<<<grid, kThreadsUG, UGSmem(R, u.nchunk, q).total(u.nbuf), ctx->stream>>>(u, tmA, tmV);
   ++ctx->launches;
   ctx->t_end();
