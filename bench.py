@@ -414,7 +414,8 @@ def main():
         if wl == "laplace3d_100_b4" and os.path.exists(tp):
             tj = json.load(open(tp))
             if dom in tj.get("kernels", {}):
-                traffic_detail = dict(tj["kernels"][dom], source=tj.get("source"))
+                traffic_detail = dict(tj["kernels"][dom])
+                traffic_detail.setdefault("source", tj.get("source"))
                 traffic = traffic_detail["dram_bytes"]
         roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
                     "frac": kern[dom]["frac"], "traffic": traffic, "traffic_detail": traffic_detail,

@@ -1,4 +1,4 @@
-"""Solve one Galeri config on the GPU: python tools/solve_demo.py Laplace3D 100 4 50 DGKS 1e-8"""
+"""Solve one Galeri config on the GPU: python tools/solve_demo.py Laplace3D 100 4 50 DGKS 1e-8 [timers|-] [reps]"""
 import sys, time, json
 import numpy as np
 sys.path.insert(0, ".")
@@ -11,7 +11,8 @@ b = int(sys.argv[3]) if len(sys.argv) > 3 else 4
 m = int(sys.argv[4]) if len(sys.argv) > 4 else 50
 ortho = sys.argv[5] if len(sys.argv) > 5 else "DGKS"
 tol = float(sys.argv[6]) if len(sys.argv) > 6 else 1e-8
-timers = len(sys.argv) > 7
+timers = len(sys.argv) > 7 and sys.argv[7] == "timers"
+reps = int(sys.argv[8]) if len(sys.argv) > 8 else 2
 dims = (nx, nx, nx) if name in ("Laplace3D", "Brick3D") else (nx, nx, 1)
 ctx = tb.Context(0)
 n, rp, ci, va = tb.galeri(name, *dims)
@@ -20,7 +21,7 @@ xe, _ = oracle.random(1, n, b)
 B = tb.MultiVec(ctx, n, b)
 Xe = tb.MultiVec.from_numpy(ctx, xe)
 op.Apply(Xe, B)
-for rep in range(2):
+for rep in range(reps):
     X = tb.MultiVec(ctx, n, b)
     mgr = tb.BlockGmresSolMgr(op, block_size=b, num_blocks=m, max_iters=-1, max_restarts=1000, tol=tol, ortho=ortho, show_timers=timers)
     l0, s0 = ctx.counters()
