@@ -53,10 +53,44 @@ def main():
         errs = dict(apply=e_apply, gram=e_gram, dot=e_dot, n2=e_n2, n1=e_n1, ninf=e_ni)
         assert max(errs.values()) <= TOL, (name, errs)
         out[name] = errs
+    # Irregular neighbour relations (every rank must walk through the same collective steps whatever its own rows couple
+    # to): (i) an upper-bidiagonal operator -- rank r needs one row of rank r+1 and nothing of rank r-1, so the halo
+    # relation is not mutual and the last rank has no ghosts at all; (ii) a tridiagonal operator whose first rank block is
+    # cut off from the rest -- rank 0 has no halo neighbour while (world >= 3) the others exchange.
+    from trilinos_b200.core import linear_partition
+    for case in ("bidiagonal", "rank0_decoupled"):
+        n = 41 * world + 5
+        lo, hi = linear_partition(n, world, rank)
+        cut = linear_partition(n, world, 0)[1]  # first row of rank 1
+        rows = []
+        for i in range(n):
+            ent = [(i, 4.0 + 0.01 * i)]
+            if i + 1 < n and not (case == "rank0_decoupled" and i + 1 == cut):
+                ent.append((i + 1, -1.0 - 0.001 * i))
+            if case == "rank0_decoupled" and i > 0 and i != cut:
+                ent.insert(0, (i - 1, -0.5))
+            rows.append(ent)
+        rp = np.zeros(n + 1, dtype=np.int32)
+        for i, ent in enumerate(rows):
+            rp[i + 1] = rp[i] + len(ent)
+        ci = np.array([c for ent in rows for c, _ in ent], dtype=np.int32)
+        va = np.array([v for ent in rows for _, v in ent], dtype=np.float64)
+        lrp = (rp[lo:hi + 1] - rp[lo]).astype(np.int32)
+        op = tb.CrsOperator(ctx, n, lo, hi, lrp, ci[rp[lo]:rp[hi]], va[rp[lo]:rp[hi]])
+        k = 3
+        xg = np.asfortranarray(np.random.default_rng(11).uniform(-1, 1, (n, k)))
+        X = tb.MultiVec.from_numpy(ctx, xg[lo:hi], n_global=n, row_offset=lo)
+        Y = tb.dist.local_multivec(ctx, n, lo, hi, k)
+        yg = oracle.spmm(rp, ci, va, xg)
+        for _ in range(3):  # (back-to-back applies: window parity, exchange numbering)
+            op.Apply(X, Y)
+        errs = dict(apply=rel(Y.to_numpy(), yg[lo:hi]), dot=rel(Y.MvDot(X), oracle.dot(yg, xg)),
+                    n2=rel(Y.MvNorm(tb.NORM_TWO), oracle.norm(yg, 1)), gram=rel(Y.MvTransMv(1.0, X), oracle.trans_mv(1.0, xg, yg)))
+        assert max(errs.values()) <= TOL, (case, errs)
+        out[case] = errs
     # one block step of DGKS (BelosDGKSOrthoManager.hpp:1400-1472, :1000-1225) on row-partitioned random data, at a size where
     # the fused update + Gram kernel and the findBasis memo are active: Gram, update (+ the next Gram from the mailbox),
     # update (+ cross products), then the column steps -- every value against the serial oracle
-    from trilinos_b200.core import linear_partition
     n, p, b = 18000 * world + 7, 40, 4
     lo, hi = linear_partition(n, world, rank)
     rng = np.random.default_rng(7)
