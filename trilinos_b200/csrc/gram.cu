@@ -55,6 +55,7 @@ struct GramArgs {
   const double* V;
   int64_t lda, ldv, n;
   int p, q;          // columns of A, columns of V handled by this launch (q <= Q)
+  int tc;            // SIMT kernel: columns of A per column block (<= kTC; the blocks are made equally wide)
   int sub;           // 64-row substeps per tile (tile rows R = 64*sub)
   int rows;          // DMMA kernel: rows per tile (R = 4 mod 16: conflict-free fragment loads)
   int nstage;
@@ -82,10 +83,12 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1)
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int R = 64 * g.sub;
-  const int ncb = (g.p + kTC - 1) / kTC;
-  // stage width: a full column block, rounded up to whole warp column groups (the TMA unit
-  // zero-fills columns >= p, so no lane ever reads shared memory that was not written)
-  const int wfull = min((g.p + CPW - 1) / CPW * CPW, kTC);
+  // Column blocks of equal width g.tc <= kTC (a multiple of CPW): p = 100 is 4 blocks of 28, 28, 28, 16 columns, not
+  // 32, 32, 32, 4 -- a 4-column last block kept 2 of the 16 consumer warps busy for as long as a full block takes
+  // (kbench p = 100: 0.86 of the HBM peak against 0.99 at p = 200).  Stage width = one block; the TMA unit zero-fills
+  // columns >= p, so no lane ever reads shared memory that was not written.
+  const int ncb = (g.p + g.tc - 1) / g.tc;
+  const int wfull = g.tc;
   const uint32_t stage_bytes = (uint32_t)((wfull + g.q) * R) * 8u;
   unsigned char* stage0 = reinterpret_cast<unsigned char*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
@@ -110,7 +113,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1)
       const uint64_t pol_a = l2_policy_evict_first();
       const uint64_t pol_v = l2_policy_evict_last();  // V is also the next kernel's operand
       for (int cb = 0; cb < ncb; ++cb) {
-        const int col0 = cb * kTC;
+        const int col0 = cb * g.tc;
         for (int t = 0; t < ntile_cta; ++t) {
           mbar_wait(&empty_bar[s], ph ^ 1u);
           const int r0 = (int)((t_begin + t) * R);
@@ -134,8 +137,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1)
     int s = 0;
     uint32_t ph = 0;
     for (int cb = 0; cb < ncb; ++cb) {
-      const int col0 = cb * kTC;
-      const int wdt = min(kTC, g.p - col0);
+      const int col0 = cb * g.tc;
+      const int wdt = min(g.tc, g.p - col0);
       // columns >= p of the last block are zero-filled by the TMA unit: no per-column predicate
       const bool active = wc * CPW < wdt;
       double acc[CPW][Q];
@@ -535,8 +538,11 @@ int launch_gram_t(Ctx* ctx, const double* A, int64_t lda, int p, const double* V
   static_assert(kTC % CPW == 0 && NW >= kTC / CPW, "one column block must fit the consumer warps");
   GramArgs g;
   g.A = A; g.V = V; g.lda = lda; g.ldv = ldv; g.n = n; g.p = p; g.q = q;
+  // equally wide column blocks: ceil(p / 32) of them, width rounded up to whole warp column groups
+  const int ncb = (p + kTC - 1) / kTC;
+  const int wfull = std::min(((p + ncb - 1) / ncb + CPW - 1) / CPW * CPW, kTC);
+  g.tc = wfull;
   // warp arrangement: as many column groups as one column block needs (power of two)
-  const int wfull = std::min((p + CPW - 1) / CPW * CPW, kTC);
   int wc_log2 = 0;
   while ((1 << wc_log2) * CPW < wfull) ++wc_log2;
   const int WR = NW >> wc_log2;
