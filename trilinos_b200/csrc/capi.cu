@@ -719,15 +719,25 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
       for (int k = 1; k <= nx; ++k)
         if (st->lazy[(size_t)(c + k)].src || st->pscale[(size_t)(c + k)] != 1.0) nx = 0;  // (not plain data: skip)
     }
+    // the step of column 1 (one previous column) also leaves X0 . Xk for the later columns, unless the block update
+    // already did (block sizes 2 and 4: the cross products of update.cu)
+    bool prev0_next = false;
+    if (p == 1 && nx > 0) {
+      double dummy;
+      int rc = 0;
+      prev0_next = !ctx->recall_dot(A->id(0), st->ver[(size_t)(c + 1)], &dummy, &rc);
+      if (rc) return rc;
+    }
+    const int nent = 2 + nx + p + (prev0_next ? nx : 0);
     FusedDots fd;
     size_t src = 0;
-    if (!fused_slot(ctx, &fd, &src, 2 + nx)) return fail(B200_ERR_ARG, "MvTimesMatAddMv: no fused slot (internal)");
+    if (!fused_slot(ctx, &fd, &src, nent)) return fail(B200_ERR_ARG, "MvTimesMatAddMv: no fused slot (internal)");
     const uint64_t old_id = mv->id(0);
     if (mv->n_local > 0)
       B200_TRY(launch_fb_step(ctx, mv->col(0), A->col(0), A->ld, p, coef, scales, nx ? st->colptr(c + 1) : nullptr,
-                              st->ld, nx, mv->n_local, alpha, beta, save_old, fd));
+                              st->ld, nx, prev0_next, mv->n_local, alpha, beta, save_old, fd));
     else  // empty row block: this rank contributes zeros (and still joins the exchange)
-      B200_TRY(launch_zero_result(ctx, fd.out, 2 + nx, fd.pub));
+      B200_TRY(launch_zero_result(ctx, fd.out, nent, fd.pub));
     mv->touch(0, 1);
     for (int i = 0; i < p; ++i) {  // the kernel stored the scaled columns
       Storage* sa = A->st.get();
@@ -746,6 +756,10 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
     ctx->remember_dot(nid, nid, 0.0, fd.seq, src);
     if (beta != 0.0) ctx->remember_dot(nid, old_id, 0.0, fd.seq, src + 1);
     for (int k = 0; k < nx; ++k) ctx->remember_dot(nid, st->ver[(size_t)(c + 1 + k)], 0.0, fd.seq, src + 2 + (size_t)k);
+    for (int i = 0; i < p; ++i) ctx->remember_dot(nid, A->id(i), 0.0, fd.seq, src + 2 + (size_t)nx + (size_t)i);
+    if (prev0_next)
+      for (int k = 0; k < nx; ++k)
+        ctx->remember_dot(A->id(0), st->ver[(size_t)(c + 1 + k)], 0.0, fd.seq, src + 2 + (size_t)nx + (size_t)p + (size_t)k);
     return 0;
   }
   B200_TRY(prep_read(A));

@@ -13,11 +13,14 @@
 //   * applies the pending normalisation factors of the previous columns (deferred MvScale, capi.cu) and writes
 //     those columns back scaled -- the arithmetic the skinny Gram kernel did (a' = fl(s a), then a' enters the sums);
 //   * stores the old Xj into a pending lazy copy (oldMXj);
-//   * emits Xj_new . Xj_new and Xj_new . Xj_old (the MvDot calls that follow), and
-//   * emits Xj_new . Xk for every LATER column k of the block: with the products X0 . Xk that the block update
-//     before findBasis leaves behind (update.cu, cross dots), these are exactly the entries of the `product`
-//     vectors of the columns still to come (scaled by the normalisation factor once that is known, which the
-//     dot memo tracks), so their MvTransMv calls are answered without a launch and without an exchange.
+//   * emits Xj_new . Xj_new and Xj_new . Xj_old (the MvDot calls that follow),
+//   * emits Xj_new . Xk for every LATER column k of the block: with the products X0 . Xk (left behind by the block
+//     update before findBasis, update.cu cross dots, for block sizes 2 and 4; by the step of column 1 otherwise),
+//     these are exactly the entries of the `product` vectors of the columns still to come (scaled by the
+//     normalisation factor once that is known, which the dot memo tracks), so their MvTransMv calls are answered
+//     without a launch and without an exchange, and
+//   * emits Xj_new . Xi for the PREVIOUS columns: the `product` of a second Gram-Schmidt pass over the same column
+//     (ICGS always makes two, BelosICGSOrthoManager.hpp:1067; DGKS when its dependency test fails, :1094).
 // Reference arithmetic of the update itself: Epetra_MultiVector::Multiply('N','N'), epetra/src/Epetra_MultiVector.cpp:1936-2083.
 #include "device_utils.cuh"
 #include "runtime.cuh"
@@ -39,20 +42,22 @@ struct FbArgs {
   const double* next; // later columns
   double* save_old;
   int64_t lda, ldn, n;
-  int p, nx, any_scale;
+  int p, nx, any_scale, prev0_next;
   double coef[kFbMax], scale[kFbMax];
   double alpha, beta;
-  FusedDots fd;       // out[0] = new.new, out[1] = new.old, out[2 + k] = new.next_k
+  // out[0] = new.new, out[1] = new.old, out[2 + k] = new.next_k, out[2 + nx + i] = new.prev_i,
+  // prev0_next: out[2 + nx + p + k] = prev_0.next_k
+  FusedDots fd;
 };
 
 template <int PMAX, int NXMAX>
-__global__ void __launch_bounds__(kFbThreads)
+__global__ void __launch_bounds__(kFbThreads, PMAX <= 4 ? 2 : 1)
     fb_step_kernel(const __grid_constant__ FbArgs f) {
-  constexpr int E = 2 + NXMAX;
+  constexpr int E = 2 + NXMAX + PMAX + NXMAX;
   const int64_t nvec = (f.n + 3) >> 2;
-  double acc[E][2];
+  double acc[E];  // (one accumulator per sum: the 4 rows of a lane's vector are folded pairwise before they enter it)
 #pragma unroll
-  for (int e = 0; e < E; ++e) acc[e][0] = acc[e][1] = 0.0;
+  for (int e = 0; e < E; ++e) acc[e] = 0.0;
   for (int64_t i = blockIdx.x * (int64_t)kFbThreads + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * kFbThreads) {
     const int64_t r = 4 * i;
     double4v va[PMAX], vn[NXMAX];
@@ -98,33 +103,47 @@ __global__ void __launch_bounds__(kFbThreads)
           vn[k].w = 0.0;
         }
     }
-    acc[0][0] = fma(o.x, o.x, acc[0][0]); acc[0][1] = fma(o.y, o.y, acc[0][1]);
-    acc[0][0] = fma(o.z, o.z, acc[0][0]); acc[0][1] = fma(o.w, o.w, acc[0][1]);
-    if (f.beta != 0.0) {
-      acc[1][0] = fma(o.x, vm.x, acc[1][0]); acc[1][1] = fma(o.y, vm.y, acc[1][1]);
-      acc[1][0] = fma(o.z, vm.z, acc[1][0]); acc[1][1] = fma(o.w, vm.w, acc[1][1]);
-    }
+    auto dot4 = [](const double4v& a, const double4v& b) {
+      return fma(a.z, b.z, a.x * b.x) + fma(a.w, b.w, a.y * b.y);
+    };
+    acc[0] += dot4(o, o);
+    if (f.beta != 0.0) acc[1] += dot4(o, vm);
 #pragma unroll
     for (int k = 0; k < NXMAX; ++k)
-      if (k < f.nx) {
-        acc[2 + k][0] = fma(o.x, vn[k].x, acc[2 + k][0]); acc[2 + k][1] = fma(o.y, vn[k].y, acc[2 + k][1]);
-        acc[2 + k][0] = fma(o.z, vn[k].z, acc[2 + k][0]); acc[2 + k][1] = fma(o.w, vn[k].w, acc[2 + k][1]);
+      if (k < f.nx) acc[2 + k] += dot4(o, vn[k]);
+    // (the previous columns: zero-filled padding rows of o keep their padding out of the sums)
+#pragma unroll
+    for (int j = 0; j < PMAX; ++j)
+      if (j < f.p) acc[2 + NXMAX + j] += dot4(o, va[j]);
+    if (f.prev0_next) {
+      double4v a0 = va[0];
+      if (r + 3 >= f.n) {
+        if (r + 1 >= f.n) a0.y = 0.0;
+        if (r + 2 >= f.n) a0.z = 0.0;
+        a0.w = 0.0;
       }
+#pragma unroll
+      for (int k = 0; k < NXMAX; ++k)
+        if (k < f.nx) acc[2 + NXMAX + PMAX + k] += dot4(a0, vn[k]);
+    }
   }
   __shared__ double sm[kFbWarps][E];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int e = 0; e < E; ++e) {
-    const double t = warp_sum(acc[e][0] + acc[e][1]);
+    const double t = warp_sum(acc[e]);
     if (lane == 0) sm[warp][e] = t;
   }
   __syncthreads();
-  const int nent = 2 + f.nx;
+  // compact the entries that exist: [2 + nx | p | nx (prev_0 . next)]
+  const int nent = 2 + f.nx + f.p + (f.prev0_next ? f.nx : 0);
   if (threadIdx.x < nent) {
-    double t = sm[0][threadIdx.x];
+    const int e = (int)threadIdx.x;
+    const int slot = e < 2 + f.nx ? e : (e < 2 + f.nx + f.p ? 2 + NXMAX + (e - 2 - f.nx) : 2 + NXMAX + PMAX + (e - 2 - f.nx - f.p));
+    double t = sm[0][slot];
 #pragma unroll
-    for (int w = 1; w < kFbWarps; ++w) t += sm[w][threadIdx.x];
-    f.fd.ws[(size_t)threadIdx.x * gridDim.x + blockIdx.x] = t;
+    for (int w = 1; w < kFbWarps; ++w) t += sm[w][slot];
+    f.fd.ws[(size_t)e * gridDim.x + blockIdx.x] = t;
   }
   if (!fold_partials_wide<kFbWarps>(f.fd.ws, f.fd.ticket, nent, gridDim.x, blockIdx.x, 1, f.fd.out)) return;
   publish_result(f.fd.pub);
@@ -133,8 +152,14 @@ __global__ void __launch_bounds__(kFbThreads)
 template <int PMAX, int NXMAX>
 int launch_fb_t(Ctx* ctx, const FbArgs& f) {
   const int64_t nvec = (f.n + 3) / 4;
+  static int per_sm = 0;  // resident CTAs per SM of this instantiation (a property of the kernel, same on every B200)
+  if (per_sm == 0) {
+    B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fb_step_kernel<PMAX, NXMAX>, kFbThreads, 0));
+    per_sm = std::max(per_sm, 1);
+  }
+  // one wave of resident CTAs (grid-stride loop inside): no second wave whose CTAs start when the first ones fold
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((nvec + 2 * kFbThreads - 1) / (2 * kFbThreads),
-                                                                 (int64_t)ctx->num_sms * 4));
+                                                                 (int64_t)ctx->num_sms * per_sm));
   fb_step_kernel<PMAX, NXMAX><<<grid, kFbThreads, 0, ctx->stream>>>(f);
   ++ctx->launches;
   B200_CUDA(cudaGetLastError());
@@ -152,15 +177,16 @@ bool fb_step_enabled() {
 }
 
 // x <- beta x + alpha A (scale .* coef), A = p <= 8 columns (leading dimension lda) whose pending factors
-// scale[0..p) are applied and written back; next = nx <= 7 later columns.  fd.out: 2 + nx sums (see FbArgs).
+// scale[0..p) are applied and written back; next = nx <= 7 later columns.  fd.out: 2 + nx + p (+ nx) sums (see FbArgs).
 int launch_fb_step(Ctx* ctx, double* x, double* A, int64_t lda, int p, const double* coef, const double* scale,
-                   const double* next, int64_t ldn, int nx, int64_t n, double alpha, double beta, double* save_old,
-                   const FusedDots& fd) {
+                   const double* next, int64_t ldn, int nx, bool prev0_next, int64_t n, double alpha, double beta,
+                   double* save_old, const FusedDots& fd) {
   if (p < 1 || p > kFbMax || nx < 0 || nx >= kFbMax)
     return fail(B200_ERR_ARG, "MvTimesMatAddMv: findBasis step with more than 8 columns (internal)");
   FbArgs f;
   f.x = x; f.A = A; f.next = next; f.save_old = save_old; f.lda = lda; f.ldn = ldn; f.n = n; f.p = p; f.nx = nx;
   f.any_scale = 0;
+  f.prev0_next = prev0_next ? 1 : 0;
   for (int j = 0; j < kFbMax; ++j) {
     f.coef[j] = j < p ? coef[j] : 0.0;
     f.scale[j] = j < p ? scale[j] : 1.0;

@@ -431,8 +431,8 @@ int launch_update(Ctx*, double* V, int64_t ldv, int q, const double* A, int64_t 
 // findbasis.cu : one-column update with pending scales, lazy copy, and dots with the later columns of the block
 bool fb_step_enabled();
 int launch_fb_step(Ctx*, double* x, double* A, int64_t lda, int p, const double* coef, const double* scale,
-                   const double* next, int64_t ldn, int nx, int64_t n, double alpha, double beta, double* save_old,
-                   const FusedDots& fd);
+                   const double* next, int64_t ldn, int nx, bool prev0_next, int64_t n, double alpha, double beta,
+                   double* save_old, const FusedDots& fd);
 // update_gram.cu : the same update; fused.out[0..2q) = the dot products, fused.out[2q + k p + col] = A^T V_new
 bool update_gram_fits(Ctx*, int p, int q, int64_t n);
 bool update_gram_always();
