@@ -40,6 +40,7 @@
 #include "runtime.cuh"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 
 namespace b200 {
@@ -82,6 +83,26 @@ struct UGSmem {
 struct UGBars {
   uint64_t full[kMaxNB][kMaxChunks], gempty[kMaxNB][kMaxChunks / kGC], xfull[kMaxNB];
 };
+
+// -DB200_UG_TRACE: CTA 0 records (globaltimer, event, tile) per warp -- the timeline behind DESIGN.md 3a
+// (tools/ug_trace.py).  Not compiled into the product.
+#ifdef B200_UG_TRACE
+__device__ unsigned long long g_ug_trace[13][4096][2];
+__device__ unsigned int g_ug_trace_n[13];
+__device__ __forceinline__ void ug_trace(int warp, int lane, int ev, int tile) {
+  if (blockIdx.x != 0 || lane != 0) return;
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  const unsigned int i = g_ug_trace_n[warp]++;
+  if (i < 4096) {
+    g_ug_trace[warp][i][0] = t;
+    g_ug_trace[warp][i][1] = ((unsigned long long)ev << 32) | (unsigned int)tile;
+  }
+}
+#define UG_TRACE(warp, lane, ev, tile) ug_trace(warp, lane, ev, tile)
+#else
+#define UG_TRACE(warp, lane, ev, tile)
+#endif
 
 #define B200_DMMA(c0, c1, a, b)                                                                \
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" \
@@ -147,6 +168,7 @@ __device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UG
     for (; c + CS <= nchunk; c += CS) {
 #pragma unroll
       for (int i = 0; i < CS; ++i) mbar_wait(&bar.full[tb][c + i], par);
+      UG_TRACE(warp, lane, 10 + c, t);
 #ifndef B200_UG_NO_UPDATE
       if (CS > 1) {
         update_batch<K, 4 * CS, NCH>(acc, tile_addr + (uint32_t)(kCW * c) * colstride, b_addr + (uint32_t)(kCW * c) * 64u,
@@ -202,6 +224,7 @@ __device__ __forceinline__ void update_role(const UGArgs& u, const UGSmem& g, UG
       }
     }
     __syncwarp();
+    UG_TRACE(warp, lane, 2, t);
     if (lane == 0) {
       mbar_arrive(&bar.xfull[tb]);
       mbar_arrive(&bar.gempty[tb][(nchunk - 1) / kGC]);
@@ -268,6 +291,7 @@ __device__ __forceinline__ void update_role_simt(const UGArgs& u, const UGSmem& 
     const uint32_t tile_addr = smem_u32(tile0) + (uint32_t)tb * g.tile_bytes;
     for (int cch = 0; cch < nchunk; ++cch) {
       mbar_wait(&bar.full[tb][cch], par);
+      UG_TRACE(warp, lane, 10 + cch, t);
 #ifndef B200_UG_NO_UPDATE
       const uint32_t ca = tile_addr + (uint32_t)(kCW * cch) * colstride, cb = b_addr + (uint32_t)(kCW * cch) * 64u;
       constexpr int CPC = kCW / NH;  // columns of a box per lane
@@ -323,6 +347,7 @@ __device__ __forceinline__ void update_role_simt(const UGArgs& u, const UGSmem& 
       }
     }
     __syncwarp();
+    UG_TRACE(warp, lane, 2, t);
     if (lane == 0) {
       mbar_arrive(&bar.xfull[tb]);
       mbar_arrive(&bar.gempty[tb][(nchunk - 1) / kGC]);
@@ -402,10 +427,12 @@ __device__ __forceinline__ void gram_role(const UGArgs& u, const UGSmem& g, UGBa
     // X_new complete: every update warp has waited for every box of the tile before it arrived here, so the boxes
     // are complete and (acquire through this barrier) visible
     mbar_wait(&bar.xfull[tb], par);
+    UG_TRACE(kNU + wg, lane, 3, t);
     const uint32_t a_addr = smem_u32(tile0) + (uint32_t)tb * g.tile_bytes + frag;
     const uint32_t x_addr = smem_u32(xbuf0) + (uint32_t)tb * g.x_bytes + frag;
 #ifndef B200_UG_NO_GRAM
     gram_groups<NCB, 0>(gacc, acc1, bar, tb, a_addr, x_addr, blk_stride, has_rhs, ng, wg, lane);
+    UG_TRACE(kNU + wg, lane, 4, t);
 #else
     __syncwarp();
     if (lane == 0) for (int grp = 0; grp <= (u.nchunk - 1) / kGC; ++grp) mbar_arrive(&bar.gempty[tb][grp]);
@@ -496,7 +523,10 @@ __global__ void __launch_bounds__(kThreadsUG, 1)
         const int r0 = (int)((t_begin + t) * R);
         unsigned char* dst = tile0 + (size_t)tb * g.tile_bytes;
         for (int c = 0; c < nchunk; ++c) {
-          if ((c & (kGC - 1)) == 0) mbar_wait(&bar.gempty[tb][c / kGC], par ^ 1u);  // both roles are done with this group
+          if ((c & (kGC - 1)) == 0) {
+            mbar_wait(&bar.gempty[tb][c / kGC], par ^ 1u);  // both roles are done with this group
+            UG_TRACE(kNU + kNG, lane, 5 + c / kGC, t);
+          }
           // the old X tile (beta != 0) travels with the LAST box (its buffer is released with the last group):
           // [column][R], the layout X_new is left in
           const bool with_x = c == nchunk - 1 && u.beta != 0.0;
@@ -643,6 +673,24 @@ int launch_update_gram(Ctx* ctx, double* V, int64_t ldv, int q, const double* A,
   ++ctx->launches;
   ctx->t_end();
   B200_CUDA(cudaGetLastError());
+#ifdef B200_UG_TRACE
+  if (const char* fn = getenv("B200_UG_TRACE_FILE")) {
+    static unsigned long long h[13][4096][2];
+    unsigned int hn[13];
+    B200_CUDA(cudaStreamSynchronize(ctx->stream));
+    B200_CUDA(cudaMemcpyFromSymbol(h, g_ug_trace, sizeof(h)));
+    B200_CUDA(cudaMemcpyFromSymbol(hn, g_ug_trace_n, sizeof(hn)));
+    unsigned int zero[13] = {};
+    B200_CUDA(cudaMemcpyToSymbol(g_ug_trace_n, zero, sizeof(zero)));
+    if (FILE* f = fopen(fn, "w")) {
+      fprintf(f, "# p=%d q=%d R=%d nbuf=%d nchunk=%d\n", p, q, R, u.nbuf, u.nchunk);
+      for (int w = 0; w < 13; ++w)
+        for (unsigned int i = 0; i < hn[w] && i < 4096; ++i)
+          fprintf(f, "%d %llu %d %d\n", w, h[w][i][0], (int)(h[w][i][1] >> 32), (int)(h[w][i][1] & 0xffffffffu));
+      fclose(f);
+    }
+  }
+#endif
   return 0;
 }
 
