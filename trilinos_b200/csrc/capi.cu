@@ -5,6 +5,7 @@
 // spmm.cu; there is no host fallback.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
@@ -1336,10 +1337,27 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
         const bool fuse = len == k && k <= kAuxSlotDoubles && fused_slot(ctx, &fd, &src, k);
         ctx->t_begin(K_SPMM, algo_bytes * len / k);
         if (pl) {
-          // interior tiles next to the put; boundary tiles (those with ghost runs) wait for the
-          // neighbours' flags themselves.  The y.y partials of both launches are folded by the last one.
+          // ONE launch: the tiles without ghost runs first (next to the put on the comm stream), then the tiles
+          // with ghost runs -- the kernel's producer warp waits for the neighbours' flags when it reaches them.
+          // (Two launches -- interior, then boundary -- cost a kernel tail + ramp per apply: B200_SPMM_SPLIT_LAUNCH=1.)
           // (kw right-hand sides per launch; every group has its own partial-sum region)
           const int64_t n1 = pl->n_int_tiles, n2 = pl->n_bnd_tiles;
+          static const bool split_launch = [] {
+            const char* e = getenv("B200_SPMM_SPLIT_LAUNCH");
+            return e && e[0] == '1';
+          }();
+          if (!split_launch) {
+            const int g = spmm_win_grid(ctx, *pl, kw, n1 + n2);
+            for (int k0 = 0; k0 < len && !rc; k0 += kw) {
+              FusedDots f2 = fd;
+              f2.out = fd.out + k0;
+              f2.ws = fd.ws + (size_t)k0 * g;
+              if (k0 + kw < len) f2.not_last();  // the last group exchanges the slot
+              rc = launch_spmm_win(ctx, op, *pl, pl->mix_tiles_d, n1 + n2, xp + (size_t)k0 * x->ld, x->ld,
+                                   yp + (size_t)k0 * y->ld, y->ld, kw, k0, fuse ? &f2 : nullptr, g, 0, g,
+                                   n2 > 0 ? &hw : nullptr, nullptr, n1);
+            }
+          } else {
           const int g1 = n1 > 0 ? spmm_win_grid(ctx, *pl, kw, n1) : 0;
           const int g2 = n2 > 0 ? spmm_win_grid(ctx, *pl, kw, n2) : 0;
           for (int pass = 0; pass < 2 && !rc; ++pass)
@@ -1357,6 +1375,7 @@ extern "C" int b200_op_apply(const b200_op* op_c, const b200_mv* x, b200_mv* y, 
                 rc = launch_spmm_win(ctx, op, *pl, pl->bnd_tiles_d, n2, xk, x->ld, yk, y->ld, kw, k0,
                                      fuse ? &f2 : nullptr, g1 + g2, g1, g1 + g2, &hw, nullptr);
             }
+          }
         } else {
           rc = launch_spmm(ctx, op, nullptr, -1, xp, x->ld, yp, y->ld, len);
           if (!rc) rc = launch_spmm_boundary(ctx, op, hw, xp, x->ld, yp, y->ld, len);

@@ -340,6 +340,7 @@ struct WinPlan {
   size_t blob_bytes = 0;
   int32_t* int_tiles_d = nullptr;  // multi-rank: tiles without / with ghost runs
   int32_t* bnd_tiles_d = nullptr;
+  int32_t* mix_tiles_d = nullptr;  // the interior tiles followed by the boundary tiles
   int64_t n_int_tiles = 0, n_bnd_tiles = 0;
   int blob_cap = 0;        // largest tile blob (bytes, multiple of 128)
   int wcap = 0;            // largest window (elements, multiple of 16)
@@ -457,7 +458,8 @@ void free_win_plan(WinPlan* plan);
 int spmm_win_grid(Ctx*, const WinPlan& pl, int k, int64_t ntiles);
 int launch_spmm_win(Ctx*, const Op* op, const WinPlan& pl, const int32_t* tile_list, int64_t ntiles,
                     const double* x, int64_t ldx, double* y, int64_t ldy, int k, int k0, const FusedDots* fused,
-                    int pstride, int part_base, int part_total, const HaloWait* wait, int* grid_out);
+                    int pstride, int part_base, int part_total, const HaloWait* wait, int* grid_out,
+                    int64_t wait_from = 0);
 // out[0..count) = 0 and hand over as a finished reduction (empty local row block)
 int launch_zero_result(Ctx*, double* out, int count, const XchgPub& pub);
 

@@ -231,6 +231,9 @@ int build_win_plan(Op* op, int R, WinPlan* plan) {
     };
     B200_TRY(up(hp.int_tiles, &plan->int_tiles_d));
     B200_TRY(up(hp.bnd_tiles, &plan->bnd_tiles_d));
+    std::vector<int32_t> mix(hp.int_tiles);
+    mix.insert(mix.end(), hp.bnd_tiles.begin(), hp.bnd_tiles.end());
+    B200_TRY(up(mix, &plan->mix_tiles_d));  // interior tiles, then boundary tiles: one launch (wait_from)
     plan->n_int_tiles = (int64_t)hp.int_tiles.size();
     plan->n_bnd_tiles = (int64_t)hp.bnd_tiles.size();
   }
@@ -248,6 +251,7 @@ void free_win_plan(WinPlan* plan) {
   cudaFree(plan->blob_d);
   cudaFree(plan->int_tiles_d);
   cudaFree(plan->bnd_tiles_d);
+  cudaFree(plan->mix_tiles_d);
   *plan = WinPlan();
 }
 
@@ -295,7 +299,9 @@ struct WinArgs {
   // part_total > 0 folds ws[k * pstride + 0 .. part_total) and publishes
   FusedDots fd;
   int pstride, part_base, part_total;
-  HaloWait wait;              // boundary launch: neighbours' flags to wait for first
+  HaloWait wait;              // neighbours' flags to wait for ...
+  int64_t wait_from;          // ... before the first list entry >= wait_from (0: before anything; the entries from
+                              // there on are the tiles with ghost runs)
 };
 
 __device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
@@ -338,7 +344,7 @@ __global__ void __launch_bounds__(R + 32)
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  if (a.wait.n > 0) {
+  if (a.wait.n > 0 && a.wait_from <= 0) {
     // peer-memory halo: the ghost block is complete once every neighbour's flag shows this apply
     if ((int)threadIdx.x < a.wait.n && !spin_acquire_sys(a.wait.flag[threadIdx.x], a.wait.seq, a.wait.err))
       give_up = 1;
@@ -372,7 +378,18 @@ __global__ void __launch_bounds__(R + 32)
       return d;
     };
     Desc nxt = load_desc(t_begin < t_end ? t_begin : 0);
+    bool halo_ready = !(a.wait.n > 0 && a.wait_from > 0);
     for (int64_t t = t_begin; t < t_end; t += t_step) {
+      if (!halo_ready && t >= a.wait_from) {
+        // One launch for interior and boundary tiles: the list holds the tiles without ghost runs first, so the
+        // neighbours' puts have the whole interior sweep to arrive; this warp waits for their flags only here, before
+        // the first window copy out of the ghost block.  (A neighbour that never arrives: the error word is set, the
+        // host reports B200_ERR_TIMEOUT; the boundary rows of this apply are then computed from stale ghosts.)
+        if (lane < a.wait.n) spin_acquire_sys(a.wait.flag[lane], a.wait.seq, a.wait.err);
+        __syncwarp();
+        asm volatile("fence.proxy.async;" ::: "memory");
+        halo_ready = true;
+      }
       const Desc d = nxt;
       if (t + t_step < t_end) nxt = load_desc(t + t_step);
       const int32_t width = d.width, nruns = d.nruns, wlen = d.wlen, gmask = d.gmask, rs = d.rs, rl = d.rl, ro = d.ro;
@@ -575,7 +592,7 @@ const WinPlan* win_plan_for(Ctx* ctx, Op* op, int k, int* rc) {
 // (x, y: first of the k columns of this launch; k0: its index in the apply's block -- the ghost block holds all of them)
 int launch_spmm_win(Ctx* ctx, const Op* op, const WinPlan& pl, const int32_t* tile_list, int64_t ntiles,
                     const double* x, int64_t ldx, double* y, int64_t ldy, int k, int k0, const FusedDots* fused,
-                    int pstride, int part_base, int part_total, const HaloWait* wait, int* grid_out) {
+                    int pstride, int part_base, int part_total, const HaloWait* wait, int* grid_out, int64_t wait_from) {
   const WinGeom g = win_geom(pl, k);
   if (g.ctas <= 0) return fail(B200_ERR_ARG, "window SpMM: geometry does not fit (internal)");
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ntiles, (int64_t)ctx->num_sms * g.ctas));
@@ -601,6 +618,7 @@ int launch_spmm_win(Ctx* ctx, const Op* op, const WinPlan& pl, const int32_t* ti
   a.part_base = part_base;
   a.part_total = part_total;
   if (wait) a.wait = *wait;
+  a.wait_from = wait_from;
   switch (k) {
     case 1: return win_launch<1>(ctx, pl, g, a, fuse, grid);
     case 2: return win_launch<2>(ctx, pl, g, a, fuse, grid);
