@@ -785,16 +785,23 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
   const size_t bytes = (size_t)p * q * sizeof(double);
   if (bytes > kStageSlotBytes)
     return fail(B200_ERR_ARG, "MvTimesMatAddMv: dense block larger than the staging slot");
-  // stage B (compact p x q) through the pinned ring, then one async H2D copy
+  // B (compact p x q).  Small blocks that go to one of the q <= 4 kernels in ONE launch travel as a kernel parameter;
+  // everything else is staged through the pinned ring and copied to the device in front of the launches.
+  const bool b_param = run_length(0, p, A, 0) == p && run_length(0, q, mv, 0) == q && q <= 4 &&
+                       (size_t)p * q <= (size_t)kBParamDoubles && mv->n_local > 0;
   const int slot = ctx->stage_next;
   ctx->stage_next = (slot + 1) % kStageSlots;
   if (ctx->stage_used[slot]) B200_CUDA(cudaEventSynchronize(ctx->stage_ev[slot]));
   double* hs = (double*)(ctx->stage_h + (size_t)slot * kStageSlotBytes);
   for (int j = 0; j < q; ++j)
     std::memcpy(hs + (size_t)j * p, B + (size_t)j * ldb, sizeof(double) * p);
-  B200_CUDA(cudaMemcpyAsync(ctx->dB, hs, bytes, cudaMemcpyHostToDevice, ctx->stream));
-  B200_CUDA(cudaEventRecord(ctx->stage_ev[slot], ctx->stream));
-  ctx->stage_used[slot] = true;
+  if (!b_param) {
+    B200_CUDA(cudaMemcpyAsync(ctx->dB, hs, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    B200_CUDA(cudaEventRecord(ctx->stage_ev[slot], ctx->stream));
+    ctx->stage_used[slot] = true;
+  } else {
+    ctx->stage_used[slot] = false;  // (the launch copies the parameter: the slot is free again at once)
+  }
   // One launch covers the whole update (A and mv both plain strided blocks)?  Then the kernel
   // also emits x_new.x_new and x_new.x_old per column — the MvDot calls DGKS makes next.
   FusedDots fd;
@@ -826,7 +833,7 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
   for (int j = 0; j < q; ++j) old_id[j] = mv->id(j);
   if (spec && mv->n_local > 0)
     B200_TRY(launch_update_gram(ctx, mv->col(0), mv->ld, q, A->col(0), A->ld, p, mv->n_local, ctx->dB, p,
-                                alpha, beta, fd));
+                                alpha, beta, fd, b_param ? hs : nullptr));
   for (int jv = 0; jv < q && !spec;) {
     const int lv = run_length(jv, q, mv, jv);
     bool first = true;
@@ -834,7 +841,7 @@ extern "C" int b200_mv_times_mat_add_mv(b200_mv* mv, double alpha, const b200_mv
       const int la = run_length(ja, p, A, ja);
       B200_TRY(launch_update(ctx, mv->col(jv), mv->ld, lv, A->col(ja), A->ld, la, mv->n_local,
                              ctx->dB + ja + (size_t)jv * p, p, alpha, first ? beta : 1.0,
-                             fuse ? &fd : nullptr, save_old));
+                             fuse ? &fd : nullptr, save_old, b_param ? hs : nullptr));
       first = false;
       ja += la;
     }

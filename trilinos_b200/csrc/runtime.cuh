@@ -79,6 +79,10 @@ struct XchgPub {
   void* win[kMaxPeers] = {};
 };
 
+// a small dense operand handed to a kernel as a parameter (no staging copy, no H2D copy in front of the launch)
+constexpr int kBParamDoubles = 1024;
+struct BParam { double v[kBParamDoubles]; };
+
 // where a kernel with a fused reduction epilogue puts its column dot products
 struct FusedDots {
   double* out = nullptr;        // where the finishing CTA stores the sums (nullptr: no epilogue): the mailbox slot
@@ -426,9 +430,11 @@ bool gram_is_skinny(int p, int q);
 // update.cu : V = alpha*A*B + beta*V with B (p x q, ld = p) already in ctx->dB + boff
 // fused != nullptr: also emit {sum new^2, sum new*old} per column into fused->out[2k], [2k+1]
 // save_old (q == 1, beta != 0 only): the kernel also stores V's old values there (a pending lazy copy of V)
+// hB != nullptr (q <= 4 only): B is NOT in device memory; the compact host copy (p x q, ld = p) travels as a kernel
+// parameter (p * q <= kBParamDoubles)
 int launch_update(Ctx*, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
                   int64_t n, const double* dB, int ldb, double alpha, double beta,
-                  const FusedDots* fused = nullptr, double* save_old = nullptr);
+                  const FusedDots* fused = nullptr, double* save_old = nullptr, const double* hB = nullptr);
 // findbasis.cu : one-column update with pending scales, lazy copy, and dots with the later columns of the block
 bool fb_step_enabled();
 int launch_fb_step(Ctx*, double* x, double* A, int64_t lda, int p, const double* coef, const double* scale,
@@ -437,9 +443,10 @@ int launch_fb_step(Ctx*, double* x, double* A, int64_t lda, int p, const double*
 // update_gram.cu : the same update; fused.out[0..2q) = the dot products, fused.out[2q + k p + col] = A^T V_new
 bool update_gram_fits(Ctx*, int p, int q, int64_t n);
 bool update_gram_always();
+// hB != nullptr: B (compact, ld = p, p * q <= kBParamDoubles) from the host as a kernel parameter instead of dB
 int launch_update_gram(Ctx*, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
                        int64_t n, const double* dB, int ldb, double alpha, double beta,
-                       const FusedDots& fused);
+                       const FusedDots& fused, const double* hB = nullptr);
 // spmm.cu
 // fused != nullptr (single rank, stream kernel only): also emit sum y(:,k)^2 into fused->out[k]
 int launch_spmm(Ctx*, const Op* op, const int32_t* rows, int64_t nrows, const double* x,

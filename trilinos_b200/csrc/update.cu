@@ -19,6 +19,7 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
 namespace b200 {
 
@@ -36,10 +37,10 @@ constexpr int kPChunk = 256;  // rows of B per shared-memory stage
 // inner products DGKS asks for right after the update (BelosDGKSOrthoManager.hpp:1091,1128,1480),
 // so those MvDot calls need neither a launch nor another pass over the column.
 template <int Q, int UNR, bool FUSE>
-__global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
-    update_kernel(double* __restrict__ V, int64_t ldv, const double* __restrict__ A, int64_t lda,
-                  int p, int64_t n, const double* __restrict__ B, int ldb, double alpha,
-                  double beta, const __grid_constant__ FusedDots fd, double* __restrict__ save_old) {
+__device__ __forceinline__ void update_body(double* __restrict__ V, int64_t ldv, const double* __restrict__ A,
+                                            int64_t lda, int p, int64_t n, const double* __restrict__ B, int ldb,
+                                            double alpha, double beta, const FusedDots& fd,
+                                            double* __restrict__ save_old) {
   __shared__ double Bs[kPChunk][Q];
   // Persistent CTAs (grid = resident capacity) walk the 512-row tiles round-robin: the fused
   // reduction's fence + ticket round trip (~2 us during which the CTA streams nothing) is paid
@@ -193,6 +194,25 @@ __global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
   if (!fold_partials_wide<kThreads / 32>(fd.ws, fd.ticket, nent, gridDim.x, blockIdx.x, 1, fd.out))
     return;
   publish_result(fd.pub);
+}
+
+template <int Q, int UNR, bool FUSE>
+__global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
+    update_kernel(double* __restrict__ V, int64_t ldv, const double* __restrict__ A, int64_t lda,
+                  int p, int64_t n, const double* __restrict__ B, int ldb, double alpha,
+                  double beta, const __grid_constant__ FusedDots fd, double* __restrict__ save_old) {
+  update_body<Q, UNR, FUSE>(V, ldv, A, lda, p, n, B, ldb, alpha, beta, fd, save_old);
+}
+
+// The same kernel with the small dense block B (p x Q, compact) as a KERNEL PARAMETER: Belos hands B over on the host,
+// and a staging copy + cudaMemcpyAsync in front of every update put a DMA operation (~3 us) on the critical path of a
+// call whose result the host waits for.  Up to kBParamDoubles entries travel with the launch instead.
+template <int Q, int UNR, bool FUSE>
+__global__ void __launch_bounds__(kThreads, (Q <= 4 ? 4 : 3))
+    update_kernel_bp(double* __restrict__ V, int64_t ldv, const double* __restrict__ A, int64_t lda, int p, int64_t n,
+                     double alpha, double beta, const __grid_constant__ FusedDots fd, double* __restrict__ save_old,
+                     const __grid_constant__ BParam bp) {
+  update_body<Q, UNR, FUSE>(V, ldv, A, lda, p, n, bp.v, p, alpha, beta, fd, save_old);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -449,7 +469,7 @@ int launch_update_dmma(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_
 template <int Q, int UNR>
 int launch_update_t(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_t lda, int p,
                     int64_t n, const double* dB, int ldb, double alpha, double beta,
-                    const FusedDots& fd, double* save_old = nullptr) {
+                    const FusedDots& fd, double* save_old = nullptr, const double* hB = nullptr) {
   const int64_t ntiles = (n + 4 * kThreads - 1) / (4 * kThreads);
   static int per_sm = 0;  // resident CTAs per SM of this instantiation (a property of the kernel, same on every B200)
   if (per_sm == 0) {
@@ -458,6 +478,17 @@ int launch_update_t(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_t l
     per_sm = std::max(per_sm, 1);
   }
   const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)ctx->num_sms * per_sm);
+  if (hB) {  // B (host, compact p x Q) travels as a kernel parameter
+    static thread_local BParam bp;  // (8 KB: not on the stack of every call)
+    std::memcpy(bp.v, hB, sizeof(double) * (size_t)p * Q);
+    if (fd.out)
+      update_kernel_bp<Q, UNR, true><<<grid, kThreads, 0, ctx->stream>>>(V, ldv, A, lda, p, n, alpha, beta, fd, save_old, bp);
+    else
+      update_kernel_bp<Q, UNR, false><<<grid, kThreads, 0, ctx->stream>>>(V, ldv, A, lda, p, n, alpha, beta, fd, save_old, bp);
+    ++ctx->launches;
+    B200_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (fd.out)
     update_kernel<Q, UNR, true><<<grid, kThreads, 0, ctx->stream>>>(V, ldv, A, lda, p, n, dB, ldb,
                                                                      alpha, beta, fd, save_old);
@@ -473,7 +504,7 @@ int launch_update_t(Ctx* ctx, double* V, int64_t ldv, const double* A, int64_t l
 
 int launch_update(Ctx* ctx, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
                   int64_t n, const double* dB, int ldb, double alpha, double beta,
-                  const FusedDots* fused, double* save_old) {
+                  const FusedDots* fused, double* save_old, const double* hB) {
   if (n <= 0 || q <= 0) return 0;
   if (save_old && (q != 1 || beta == 0.0))
     return fail(B200_ERR_ARG, "MvTimesMatAddMv: save_old needs a one-column read-modify-write update (internal)");
@@ -505,9 +536,10 @@ int launch_update(Ctx* ctx, double* V, int64_t ldv, int q, const double* A, int6
           break;
         }
         rc = launch_update_t<8, 4>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
-      case 4: rc = launch_update_t<4, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
-      case 2: rc = launch_update_t<2, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd); break;
-      default: rc = launch_update_t<1, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd, save_old); break;
+      // (hB: the compact host copy of B, when the caller did not upload it: columns k0 .. of it for this launch)
+      case 4: rc = launch_update_t<4, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd, nullptr, hB ? hB + (size_t)k0 * p : nullptr); break;
+      case 2: rc = launch_update_t<2, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd, nullptr, hB ? hB + (size_t)k0 * p : nullptr); break;
+      default: rc = launch_update_t<1, 8>(ctx, Vk, ldv, A, lda, p, n, Bk, ldb, alpha, beta, fd, save_old, hB ? hB + (size_t)k0 * p : nullptr); break;
     }
     k0 += step;
   }

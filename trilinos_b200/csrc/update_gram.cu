@@ -42,6 +42,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 
 namespace b200 {
 
@@ -66,6 +67,7 @@ struct UGArgs {
   int p, q, ldb, rows, nchunk, nbuf, dmma_update;
   double alpha, beta;
   FusedDots fd;     // out[0 .. 2q): dot products, out[2q + k p + col]: (A^T V_new)(col, k)
+  BParam bval;      // B == nullptr: the dense block travels with the launch (compact p x q)
 };
 
 // shared-memory geometry, the same on host and device
@@ -500,7 +502,7 @@ __global__ void __launch_bounds__(kThreadsUG, 1)
 
   for (int e = threadIdx.x; e < nchunk * kCW * 8; e += kThreadsUG) {
     const int j = e >> 3, c = e & 7;
-    Bs[e] = (j < p && c < q) ? u.B[(size_t)c * u.ldb + j] : 0.0;
+    Bs[e] = (j < p && c < q) ? (u.B ? u.B[(size_t)c * u.ldb + j] : u.bval.v[c * p + j]) : 0.0;
   }
   if (threadIdx.x == 0) {
     for (int b = 0; b < u.nbuf; ++b) {
@@ -638,9 +640,14 @@ bool update_gram_always() { return spec_mode() >= 2; }
 // per column and fd.out[2q + k p + col] = sum_rows A(:, col) V_new(:, k)
 int launch_update_gram(Ctx* ctx, double* V, int64_t ldv, int q, const double* A, int64_t lda, int p,
                        int64_t n, const double* dB, int ldb, double alpha, double beta,
-                       const FusedDots& fd) {
-  UGArgs u;
-  u.V = V; u.B = dB; u.ldv = ldv; u.n = n; u.p = p; u.q = q; u.ldb = ldb;
+                       const FusedDots& fd, const double* hB) {
+  static thread_local UGArgs u;  // (holds the 8 KB parameter copy of B: not on the stack of every call)
+  u.V = V; u.B = dB;
+  if (hB) {
+    if ((size_t)p * q > (size_t)kBParamDoubles) return fail(B200_ERR_ARG, "MvTimesMatAddMv: dense block too large for a kernel parameter (internal)");
+    u.B = nullptr;
+    std::memcpy(u.bval.v, hB, sizeof(double) * (size_t)p * q);
+  } u.ldv = ldv; u.n = n; u.p = p; u.q = q; u.ldb = ldb;
   u.alpha = alpha; u.beta = beta; u.fd = fd;
   int R = ug_pick_rows(p, q, n, ctx->num_sms);
   if (const char* e = getenv("B200_UG_ROWS")) R = atoi(e);
