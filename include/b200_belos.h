@@ -174,6 +174,20 @@ int b200_mv_copy_from_host(b200_mv* mv, const double* host, int64_t ldh);
 /* raw device pointer of column j and the leading dimension (harness / tests) */
 int b200_mv_device_ptr(const b200_mv* mv, int col, void** ptr, int64_t* ld);
 
+/* out[j] <- sum_i x(i,j)*y(i,j), j < ncols: the local arithmetic of b200_mv_dot WITHOUT any allocation.
+ * No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Needs no context.
+ * x, y (column-major, leading dimensions ldx, ldy >= n) and out (ncols doubles) are DEVICE pointers on the
+ * caller's current device; stream is a cudaStream_t (NULL = default stream); the call is stream-ordered and
+ * does not synchronise.  The per-CTA partial sums live in a static __device__ array of 262400 bytes that
+ * every GPU loading the library holds until exit: ncols > B200_NOALLOC_MAX_COLS is rejected with
+ * B200_ERR_ARG (rows are not limited).  All calls on a device share that array: calls that overlap on the
+ * GPU (different streams or threads) race -- serialise them.  Single process: a multi-rank caller sums
+ * out[] over the ranks itself. */
+#define B200_NOALLOC_MAX_COLS 32
+int b200_dot_noalloc(const double* x, int64_t ldx, const double* y, int64_t ldy, int64_t n, int ncols,
+                     double* out, void* stream);
+
 /* ----------------------------------------------------------------- operator
  * Replaces Epetra_CrsMatrix::Multiply(false, X, Y)
  * (epetra/src/Epetra_CrsMatrix.cpp:3107-3285; kernels GeneralMV :3315-3413,

@@ -82,6 +82,7 @@ _SIGS = {
     "b200_mv_copy_to_host": (C.c_int, [vp, P(c_dbl), c_i64]),
     "b200_mv_copy_from_host": (C.c_int, [vp, P(c_dbl), c_i64]),
     "b200_mv_device_ptr": (C.c_int, [vp, C.c_int, P(vp), P(c_i64)]),
+    "b200_dot_noalloc": (C.c_int, [vp, c_i64, vp, c_i64, c_i64, C.c_int, vp, vp]),
     "b200_op_create_csr": (C.c_int, [vp, c_i64, c_i64, c_i64, P(c_i32), P(c_i64), P(c_dbl), P(vp)]),
     "b200_op_destroy": (C.c_int, [vp]),
     "b200_op_apply": (C.c_int, [vp, vp, vp, C.c_int]),
