@@ -345,6 +345,7 @@ struct WinPlan {
   int32_t* int_tiles_d = nullptr;  // multi-rank: tiles without / with ghost runs
   int32_t* bnd_tiles_d = nullptr;
   int32_t* mix_tiles_d = nullptr;  // the interior tiles followed by the boundary tiles
+  WinTile* tiles_mix_d = nullptr;  // the descriptors in that order (what the merged launch reads)
   int64_t n_int_tiles = 0, n_bnd_tiles = 0;
   int blob_cap = 0;        // largest tile blob (bytes, multiple of 128)
   int wcap = 0;            // largest window (elements, multiple of 16)

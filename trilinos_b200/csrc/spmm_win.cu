@@ -234,6 +234,15 @@ int build_win_plan(Op* op, int R, WinPlan* plan) {
     std::vector<int32_t> mix(hp.int_tiles);
     mix.insert(mix.end(), hp.bnd_tiles.begin(), hp.bnd_tiles.end());
     B200_TRY(up(mix, &plan->mix_tiles_d));  // interior tiles, then boundary tiles: one launch (wait_from)
+    // ... and the descriptors themselves in that order: the merged launch reads tiles_mix_d[t] directly.  (Through the
+    // index list the producer warp had two dependent global loads per tile -- list entry, then descriptor -- on a
+    // chain that is only one tile ahead: about the tile period itself (~1.6 us), and the multi-rank apply ran ~27 %
+    // slower than the same rows on one rank: 156 vs 113 us at 4M rows, profiles/r2_apply_ab_n2_s34.txt.)
+    std::vector<WinTile> tmix(mix.size());
+    for (size_t i = 0; i < mix.size(); ++i) tmix[i] = hp.tiles[(size_t)mix[i]];
+    B200_CUDA(cudaMalloc((void**)&plan->tiles_mix_d, std::max<size_t>(1, tmix.size()) * sizeof(WinTile)));
+    if (!tmix.empty())
+      B200_CUDA(cudaMemcpy(plan->tiles_mix_d, tmix.data(), tmix.size() * sizeof(WinTile), cudaMemcpyHostToDevice));
     plan->n_int_tiles = (int64_t)hp.int_tiles.size();
     plan->n_bnd_tiles = (int64_t)hp.bnd_tiles.size();
   }
@@ -252,6 +261,7 @@ void free_win_plan(WinPlan* plan) {
   cudaFree(plan->int_tiles_d);
   cudaFree(plan->bnd_tiles_d);
   cudaFree(plan->mix_tiles_d);
+  cudaFree(plan->tiles_mix_d);
   *plan = WinPlan();
 }
 
@@ -601,6 +611,14 @@ int launch_spmm_win(Ctx* ctx, const Op* op, const WinPlan& pl, const int32_t* ti
   WinArgs a;
   a.tiles = pl.tiles_d;
   a.tile_list = tile_list;
+  static const bool mix_by_list = [] {  // B200_SPMM_MIX_LIST=1: the merged launch goes through the index list (A/B)
+    const char* e = getenv("B200_SPMM_MIX_LIST");
+    return e && e[0] == '1';
+  }();
+  if (tile_list && tile_list == pl.mix_tiles_d && pl.tiles_mix_d && !mix_by_list) {
+    a.tiles = pl.tiles_mix_d;  // the descriptors in list order: no indirection
+    a.tile_list = nullptr;
+  }
   a.ntiles = ntiles;
   a.blob = pl.blob_d;
   a.x = x;
