@@ -60,3 +60,12 @@ def test_noalloc_dot_rejects_sizes_beyond_the_static_array(ctx):
     with pytest.raises(B200Error):
         check(lib.b200_dot_noalloc(pa, lda, pa, lda, -1, 1, po, ctx.stream))
     check(lib.b200_dot_noalloc(pa, lda, pa, lda, 64, 0, po, ctx.stream))  # nothing to do is not an error
+
+
+def test_noalloc_dot_size_check_needs_no_device():
+    """The limit is checked before anything touches CUDA: same answer on a box without a GPU."""
+    buf = (C.c_double * 4)()
+    p = C.cast(buf, C.c_void_p)
+    with pytest.raises(B200Error, match="at most 32"):
+        check(lib.b200_dot_noalloc(p, 4, p, 4, 4, MAX_COLS + 1, p, None))
+    assert lib.b200_dot_noalloc(p, 4, p, 4, 4, 0, p, None) == 0
