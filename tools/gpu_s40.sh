@@ -3,7 +3,7 @@
 N=${1:-4}
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
-timeout 280 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29640 \
+timeout ${B200_RUN_LIMIT:-280} python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29640 \
   bench.py --gpus $N --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/s40_bench_n$N.json 2> gpurun_out/s40_bench_n$N.err; echo "bench rc=$?"
 python - $N <<'PY'
 import json, sys
